@@ -1,0 +1,594 @@
+// Context, rank bootstrap (CUDA IPC), update_halo and gather entry points of libigg_b200.
+//
+// Ownership mirrors the reference's module-level buffer/stream singletons (ref: src/update_halo.jl:103-107,
+// src/CUDAExt/update_halo.jl:19-25,148-151) but lives in an explicit context: the context owns the control segment
+// (arrival flags + counters), the double-buffered receive staging, cached plans and peer mappings; user arrays are
+// only borrowed for the duration of a call.
+#include <cuda_runtime.h>
+#include <unistd.h>
+
+#include <cstdlib>
+#include <memory>
+#include <mutex>
+
+#include "ctrl_shm.h"
+#include "igg_internal.h"
+
+#define CU(call)                                                                                      \
+    do {                                                                                              \
+        cudaError_t e_ = (call);                                                                      \
+        if (e_ != cudaSuccess) return igg::fail(IGG_ERR_CUDA, "%s failed: %s", #call, cudaGetErrorString(e_)); \
+    } while (0)
+
+namespace igg {
+
+constexpr uint64_t kBlobMagic = 0x31424747495f4742ull;   // "BG_IGGB1"
+constexpr size_t kCtrlBytes = 8192;                      // 27 flags * 128 B + counters
+constexpr size_t kCountersOff = 4096;
+
+struct BootBlob {
+    uint64_t magic;
+    uint64_t proc_nonce;          // equal for ranks living in the same process (raw pointers are valid then)
+    int32_t rank, device;
+    cudaIpcMemHandle_t ctrl_handle;
+    uint64_t ctrl_ptr;
+    char shm_name[64];
+    char pad[96];
+};
+static_assert(sizeof(BootBlob) == 256, "BootBlob size");
+
+struct SegPayload {               // travels through the mailbox when a segment is (re)allocated
+    uint64_t proc_nonce;
+    int32_t device, status;
+    cudaIpcMemHandle_t handle;
+    uint64_t ptr;
+    int64_t bytes;                // staging: bytes of ONE half; gather: buffer bytes
+    char msg[kMailPayload - 96];
+};
+static_assert(sizeof(SegPayload) == kMailPayload, "SegPayload size");
+
+struct PeerSeg {
+    char* ptr = nullptr;
+    bool ipc = false;
+    int64_t bytes = 0;
+    uint64_t raw = 0;             // the owner's own address of the segment (identity check)
+};
+
+struct Peer {
+    uint64_t proc_nonce = 0;
+    int device = -1;
+    PeerSeg ctrl, staging, gather;
+};
+
+static uint64_t process_nonce() {
+    static uint64_t nonce = [] {
+        uint64_t n = 0;
+        FILE* f = fopen("/dev/urandom", "rb");
+        if (f) { if (fread(&n, sizeof(n), 1, f) != 1) n = 0; fclose(f); }
+        if (!n) n = ((uint64_t)getpid() << 32) ^ 0x9e3779b97f4a7c15ull;
+        return n;
+    }();
+    return nonce;
+}
+
+}  // namespace igg
+
+using namespace igg;
+
+struct igg_ctx {
+    igg_grid_desc g;
+    int device = 0;
+    int mode = IGG_MODE_IPC_1PHASE;
+    char* ctrl = nullptr;                       // device: flags at 0, counters at kCountersOff
+    char* staging = nullptr;                    // device: two halves
+    int64_t staging_half = 0;
+    int* h_status = nullptr;                    // host-mapped status word
+    int* d_status = nullptr;
+    ControlPlane cp;
+    std::string shm_name;
+    std::vector<Peer> peers;
+    bool bootstrapped = false;
+    std::vector<std::unique_ptr<Plan>> plans;
+    unsigned long long epoch[IGG_NOFFSETS] = {0};
+    int max_blocks = 0;
+    int64_t launches = 0;
+    cudaStream_t last_stream = nullptr;
+    cudaEvent_t last_event = nullptr;
+    bool have_last = false;
+    unsigned long long timeout_ns = 20ull * 1000000000ull;
+    struct PtrEntry { const void* user = nullptr; void* resolved = nullptr; };
+    PtrEntry ptr_cache[64];
+    // gather
+    char* gather_buf = nullptr;   int64_t gather_bytes = 0;       // root: device image of A_global (peer mapped)
+    char* gather_src = nullptr;   int64_t gather_src_bytes = 0;   // staging for host-resident A
+    TileRec* d_gather_tiles = nullptr; int gather_tiles_cap = 0;
+    // NCCL comparison path (nccl_path.cu)
+    void* nccl = nullptr;
+};
+
+namespace igg {
+int nccl_update_halo(igg_ctx* ctx, int nfields, const igg_field* fields, int dims_mask, const int* order, int norder,
+                     cudaStream_t stream);
+void nccl_destroy(igg_ctx* ctx);
+}
+
+// ---- helpers -----------------------------------------------------------------------------------------------------
+
+static int open_segment(igg_ctx* ctx, const Peer& peer, const cudaIpcMemHandle_t& h, uint64_t raw_ptr, PeerSeg& out) {
+    if (peer.proc_nonce == process_nonce()) {         // same process: the raw pointer is valid, just enable P2P
+        if (peer.device != ctx->device) {
+            cudaError_t e = cudaDeviceEnablePeerAccess(peer.device, 0);
+            if (e == cudaErrorPeerAccessAlreadyEnabled) cudaGetLastError();
+            else if (e != cudaSuccess) return fail(IGG_ERR_IPC, "cudaDeviceEnablePeerAccess(%d) failed: %s", peer.device, cudaGetErrorString(e));
+        }
+        out.ptr = reinterpret_cast<char*>(raw_ptr);
+        out.ipc = false;
+        return IGG_OK;
+    }
+    void* p = nullptr;
+    cudaError_t e = cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess);
+    if (e != cudaSuccess) return fail(IGG_ERR_IPC, "cudaIpcOpenMemHandle failed: %s", cudaGetErrorString(e));
+    out.ptr = static_cast<char*>(p);
+    out.ipc = true;
+    return IGG_OK;
+}
+
+static void close_segment(PeerSeg& s) {
+    if (s.ptr && s.ipc) cudaIpcCloseMemHandle(s.ptr);
+    s = PeerSeg();
+}
+
+// Collective (re)allocation of a peer-visible segment: everyone frees the old one, allocates `bytes`, and learns
+// everyone else's new mapping through the mailbox.  `which`: 0 = staging, 1 = gather buffer (root only allocates).
+static int exchange_segment(igg_ctx* ctx, int which, int64_t my_bytes, int status, const char* msg,
+                            std::vector<SegPayload>& all_out) {
+    SegPayload mine;
+    std::memset(&mine, 0, sizeof(mine));
+    mine.proc_nonce = process_nonce();
+    mine.device = ctx->device;
+    mine.status = status;
+    if (msg) snprintf(mine.msg, sizeof(mine.msg), "%s", msg);
+    char* ptr = (which == 0) ? ctx->staging : ctx->gather_buf;
+    if (ptr && my_bytes > 0) {
+        CU(cudaIpcGetMemHandle(&mine.handle, ptr));
+        mine.ptr = reinterpret_cast<uint64_t>(ptr);
+    }
+    mine.bytes = my_bytes;
+    std::vector<char> all;
+    int rc = ctx->cp.allgather(&mine, all);
+    if (rc) return rc;
+    all_out.resize(ctx->g.nprocs);
+    std::memcpy(all_out.data(), all.data(), all.size());
+    return IGG_OK;
+}
+
+static int grow_staging(igg_ctx* ctx, int64_t need_half) {
+    // Nobody may still write into / read from the old staging: my kernels are done, then everyone's are.
+    CU(cudaDeviceSynchronize());
+    int rc = ctx->cp.barrier();
+    if (rc) return rc;
+    for (auto& p : ctx->peers) close_segment(p.staging);
+    rc = ctx->cp.barrier();                     // every mapping of my old staging is closed before I free it
+    if (rc) return rc;
+    if (ctx->staging) { CU(cudaFree(ctx->staging)); ctx->staging = nullptr; }
+    int64_t half = std::max<int64_t>(need_half + need_half / 4, 1 << 20);
+    half = (half + 0xfffff) & ~int64_t(0xfffff);
+    CU(cudaMalloc(&ctx->staging, (size_t)(2 * half)));
+    ctx->staging_half = half;
+    std::vector<SegPayload> all;
+    rc = exchange_segment(ctx, 0, half, 0, nullptr, all);
+    if (rc) return rc;
+    for (int r = 0; r < ctx->g.nprocs; ++r) {
+        if (r == ctx->g.me) continue;
+        rc = open_segment(ctx, ctx->peers[r], all[r].handle, all[r].ptr, ctx->peers[r].staging);
+        if (rc) return rc;
+        ctx->peers[r].staging.bytes = all[r].bytes;
+    }
+    return IGG_OK;
+}
+
+// Resolves a user pointer to an address the kernels can use: device memory as is, mapped page-locked host memory
+// through its device alias.  Pageable host memory is rejected (no CPU fallback, no hidden copies in update_halo).
+static int resolve_pointer(igg_ctx* ctx, const void* p, void** out, bool* is_host) {
+    igg_ctx::PtrEntry& ce = ctx->ptr_cache[((uintptr_t)p >> 8) & 63];
+    if (!is_host && ce.user == p) { *out = ce.resolved; return IGG_OK; }
+    cudaPointerAttributes a;
+    cudaError_t e = cudaPointerGetAttributes(&a, p);
+    if (e != cudaSuccess) { cudaGetLastError(); return fail(IGG_ERR_CUDA, "cudaPointerGetAttributes failed: %s", cudaGetErrorString(e)); }
+    if (a.type == cudaMemoryTypeDevice || a.type == cudaMemoryTypeManaged) {
+        *out = const_cast<void*>(p);
+        if (is_host) *is_host = false;
+        ce.user = p; ce.resolved = *out;
+        return IGG_OK;
+    }
+    if (a.type == cudaMemoryTypeHost && a.devicePointer) {
+        *out = a.devicePointer;
+        if (is_host) *is_host = true;
+        ce.user = p; ce.resolved = *out;
+        return IGG_OK;
+    }
+    return fail(IGG_ERR_UNSUPPORTED,
+                "pointer %p is pageable host memory: pass device memory or page-locked (pinned/registered) host memory.", p);
+}
+
+static Plan* find_or_build_plan(igg_ctx* ctx, int nfields, const igg_field* fields, int dims_mask, int* rc_out) {
+    for (auto& up : ctx->plans) {
+        Plan* p = up.get();
+        if (p->dims_mask != dims_mask || (int)p->key.size() != nfields) continue;
+        bool same = true;
+        for (int i = 0; i < nfields && same; ++i) {
+            const FieldKey& k = p->key[i];
+            const igg_field& f = fields[i];
+            same = k.elsize == f.elsize && k.ndims == f.ndims && k.align == (int32_t)((uintptr_t)f.ptr % 16);
+            for (int d = 0; d < 3 && same; ++d) same = k.size[d] == f.size[d] && k.hw[d] == f.halowidths[d];
+        }
+        if (same) { *rc_out = IGG_OK; return p; }
+    }
+    std::unique_ptr<Plan> plan(new Plan());
+    int rc = build_plan(ctx->g, nfields, fields, dims_mask, *plan);
+    if (rc) { *rc_out = rc; return nullptr; }
+    if (!plan->tiles.empty()) {
+        cudaError_t e = cudaMalloc(&plan->d_tiles, plan->tiles.size() * sizeof(TileRec));
+        if (e == cudaSuccess)
+            e = cudaMemcpy(plan->d_tiles, plan->tiles.data(), plan->tiles.size() * sizeof(TileRec), cudaMemcpyHostToDevice);
+        if (e != cudaSuccess) { *rc_out = fail(IGG_ERR_CUDA, "plan upload failed: %s", cudaGetErrorString(e)); return nullptr; }
+        plan->grid = (int)std::min<int64_t>((int64_t)plan->tiles.size(), ctx->max_blocks);
+    }
+    if (ctx->plans.size() >= 64) {   // bound the cache (fields of ever-changing shapes)
+        if (ctx->plans.front()->d_tiles) { cudaDeviceSynchronize(); cudaFree(ctx->plans.front()->d_tiles); }
+        ctx->plans.erase(ctx->plans.begin());
+    }
+    ctx->plans.push_back(std::move(plan));
+    *rc_out = IGG_OK;
+    return ctx->plans.back().get();
+}
+
+static void order_after_previous(igg_ctx* ctx, cudaStream_t stream) {
+    // Calls on one context must execute in issue order (the staging double-buffer relies on it).
+    if (ctx->have_last && ctx->last_stream != stream) cudaStreamWaitEvent(stream, ctx->last_event, 0);
+}
+
+static void remember_launch(igg_ctx* ctx, cudaStream_t stream) {
+    cudaEventRecord(ctx->last_event, stream);
+    ctx->last_stream = stream;
+    ctx->have_last = true;
+    ctx->launches += 1;
+}
+
+static int check_status(igg_ctx* ctx) {
+    if (*ctx->h_status != 0) {
+        const int s = *ctx->h_status;
+        *ctx->h_status = 0;
+        return fail(s, "update_halo: a neighbour rank did not deliver its halo within %.1f s (device-side time-out).",
+                    ctx->timeout_ns * 1e-9);
+    }
+    return IGG_OK;
+}
+
+// ---- C ABI -------------------------------------------------------------------------------------------------------
+extern "C" {
+
+int igg_create(const igg_grid_desc* desc, igg_ctx** out) {
+    if (!desc || !out) return fail(IGG_ERR_ARG, "igg_create: NULL argument.");
+    int rc = check_grid(*desc);
+    if (rc) return rc;
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0) {
+        cudaGetLastError();
+        return fail(IGG_ERR_CUDA, "No usable CUDA device (%s); libigg_b200 has no CPU fallback.", cudaGetErrorString(e));
+    }
+    // ref: src/select_device.jl:30
+    if (desc->device < 0 || desc->device >= ndev)
+        return fail(IGG_ERR_ARG, "More processes have been launched per node than there are GPUs available.");
+    std::unique_ptr<igg_ctx> ctx(new igg_ctx());
+    ctx->g = *desc;
+    ctx->device = desc->device;
+    CU(cudaSetDevice(ctx->device));
+    CU(cudaMalloc(&ctx->ctrl, kCtrlBytes));
+    CU(cudaMemset(ctx->ctrl, 0, kCtrlBytes));
+    CU(cudaHostAlloc(&ctx->h_status, sizeof(int), cudaHostAllocMapped));
+    *ctx->h_status = 0;
+    CU(cudaHostGetDevicePointer(&ctx->d_status, ctx->h_status, 0));
+    CU(cudaEventCreateWithFlags(&ctx->last_event, cudaEventDisableTiming));
+    ctx->max_blocks = halo_kernel_max_coresident_blocks(ctx->device);
+    if (ctx->max_blocks <= 0) return fail(IGG_ERR_CUDA, "occupancy query for the halo kernel failed (was the library built for sm_100a?): %s", cudaGetErrorString(cudaGetLastError()));
+    if (const char* t = getenv("IGG_DEVICE_TIMEOUT_S")) ctx->timeout_ns = (unsigned long long)(atof(t) * 1e9);
+    ctx->peers.resize(desc->nprocs);
+    if (desc->nprocs > 1) {
+        rc = ctx->cp.create(desc->me, desc->nprocs, ctx->shm_name);
+        if (rc) return rc;
+    } else {
+        ctx->bootstrapped = true;
+    }
+    CU(cudaDeviceSynchronize());
+    *out = ctx.release();
+    return IGG_OK;
+}
+
+int igg_destroy(igg_ctx* ctx) {
+    if (!ctx) return IGG_OK;
+    cudaSetDevice(ctx->device);
+    cudaDeviceSynchronize();
+    if (ctx->g.nprocs > 1 && ctx->cp.attached()) ctx->cp.barrier();   // nobody is still writing into my segments
+    nccl_destroy(ctx);
+    for (auto& p : ctx->peers) { close_segment(p.ctrl); close_segment(p.staging); close_segment(p.gather); }
+    for (auto& pl : ctx->plans) if (pl->d_tiles) cudaFree(pl->d_tiles);
+    if (ctx->staging) cudaFree(ctx->staging);
+    if (ctx->gather_buf) cudaFree(ctx->gather_buf);
+    if (ctx->gather_src) cudaFree(ctx->gather_src);
+    if (ctx->d_gather_tiles) cudaFree(ctx->d_gather_tiles);
+    if (ctx->ctrl) cudaFree(ctx->ctrl);
+    if (ctx->h_status) cudaFreeHost(ctx->h_status);
+    if (ctx->last_event) cudaEventDestroy(ctx->last_event);
+    ctx->cp.close();
+    delete ctx;
+    return IGG_OK;
+}
+
+size_t igg_bootstrap_size(void) { return sizeof(BootBlob); }
+
+int igg_bootstrap_export(igg_ctx* ctx, void* blob) {
+    if (!ctx || !blob) return fail(IGG_ERR_ARG, "igg_bootstrap_export: NULL argument.");
+    CU(cudaSetDevice(ctx->device));
+    BootBlob b;
+    std::memset(&b, 0, sizeof(b));
+    b.magic = kBlobMagic;
+    b.proc_nonce = process_nonce();
+    b.rank = ctx->g.me;
+    b.device = ctx->device;
+    CU(cudaIpcGetMemHandle(&b.ctrl_handle, ctx->ctrl));
+    b.ctrl_ptr = reinterpret_cast<uint64_t>(ctx->ctrl);
+    snprintf(b.shm_name, sizeof(b.shm_name), "%s", ctx->shm_name.c_str());
+    std::memcpy(blob, &b, sizeof(b));
+    return IGG_OK;
+}
+
+int igg_bootstrap_import(igg_ctx* ctx, const void* all_blobs, int nprocs) {
+    if (!ctx || !all_blobs) return fail(IGG_ERR_ARG, "igg_bootstrap_import: NULL argument.");
+    if (nprocs != ctx->g.nprocs) return fail(IGG_ERR_ARG, "igg_bootstrap_import: got %d blobs for %d ranks.", nprocs, ctx->g.nprocs);
+    if (ctx->bootstrapped) return IGG_OK;
+    CU(cudaSetDevice(ctx->device));
+    const BootBlob* blobs = static_cast<const BootBlob*>(all_blobs);
+    std::vector<std::string> names(nprocs);
+    for (int r = 0; r < nprocs; ++r) {
+        BootBlob b;
+        std::memcpy(&b, blobs + r, sizeof(b));
+        if (b.magic != kBlobMagic || b.rank != r) return fail(IGG_ERR_ARG, "igg_bootstrap_import: blob %d is corrupt or out of rank order.", r);
+        names[r] = b.shm_name;
+        if (r == ctx->g.me) continue;
+        ctx->peers[r].proc_nonce = b.proc_nonce;
+        ctx->peers[r].device = b.device;
+        int rc = open_segment(ctx, ctx->peers[r], b.ctrl_handle, b.ctrl_ptr, ctx->peers[r].ctrl);
+        if (rc) return rc;
+    }
+    int rc = ctx->cp.attach(names);
+    if (rc) return rc;
+    ctx->bootstrapped = true;
+    return IGG_OK;
+}
+
+int igg_set_mode(igg_ctx* ctx, int mode) {
+    if (!ctx) return fail(IGG_ERR_ARG, "igg_set_mode: NULL context.");
+    if (mode != IGG_MODE_IPC_1PHASE && mode != IGG_MODE_NCCL_3PHASE) return fail(IGG_ERR_ARG, "igg_set_mode: unknown mode %d.", mode);
+    if (mode == IGG_MODE_NCCL_3PHASE && ctx->g.nprocs > 1 && !ctx->nccl)
+        return fail(IGG_ERR_STATE, "igg_set_mode: call igg_nccl_init before selecting IGG_MODE_NCCL_3PHASE.");
+    ctx->mode = mode;
+    return IGG_OK;
+}
+
+int igg_update_halo(igg_ctx* ctx, int nfields, const igg_field* fields_in, const int* dims_order, int ndims_order,
+                    void* stream_v, int flags) {
+    if (!ctx || !fields_in) return fail(IGG_ERR_ARG, "igg_update_halo: NULL argument.");
+    if (!ctx->bootstrapped) return fail(IGG_ERR_STATE, "igg_update_halo: call igg_bootstrap_import first (nprocs > 1).");
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_v);
+    int dims_mask;
+    int rc = dims_mask_from_order(dims_order, ndims_order, &dims_mask);
+    if (rc) return rc;
+    rc = check_fields(ctx->g, nfields, fields_in);
+    if (rc) return rc;
+    CU(cudaSetDevice(ctx->device));
+
+    igg_field fields[IGG_MAX_FIELDS];
+    for (int i = 0; i < nfields; ++i) {
+        fields[i] = fields_in[i];
+        rc = resolve_pointer(ctx, fields_in[i].ptr, &fields[i].ptr, nullptr);
+        if (rc) return rc;
+    }
+
+    if (ctx->mode == IGG_MODE_NCCL_3PHASE && ctx->g.nprocs > 1) {
+        rc = nccl_update_halo(ctx, nfields, fields, dims_mask, dims_order, ndims_order, stream);
+        if (rc) return rc;
+        if (!(flags & IGG_ASYNC)) CU(cudaStreamSynchronize(stream));
+        return IGG_OK;
+    }
+
+    Plan* plan = find_or_build_plan(ctx, nfields, fields, dims_mask, &rc);
+    if (!plan) return rc;
+    if (plan->tiles.empty()) return IGG_OK;                       // e.g. one rank, nothing periodic
+    if (plan->active_mask && plan->staging_bytes > ctx->staging_half) {
+        rc = grow_staging(ctx, plan->staging_bytes);
+        if (rc) return rc;
+    }
+
+    KParams p;
+    std::memset(&p, 0, sizeof(p));
+    p.tiles = plan->d_tiles;
+    p.n_tiles = (int32_t)plan->tiles.size();
+    p.n_push_tiles = plan->n_push_tiles;
+    for (int i = 0; i < nfields; ++i) p.field[i] = fields[i].ptr;
+    p.local_flag = reinterpret_cast<const unsigned long long*>(ctx->ctrl);
+    p.push_count = reinterpret_cast<unsigned int*>(ctx->ctrl + kCountersOff);
+    p.status = ctx->d_status;
+    p.timeout_ns = ctx->timeout_ns;
+    for (int oi = 0; oi < IGG_NOFFSETS; ++oi) {
+        if (!((plan->active_mask >> oi) & 1u)) continue;
+        const Peer& peer = ctx->peers[plan->peer[oi]];
+        const unsigned long long ep = ++ctx->epoch[oi];
+        const int par = (int)(ep & 1ull);
+        p.epoch[oi] = ep;
+        p.expected[oi] = plan->expected[oi];
+        p.push_base[oi] = peer.staging.ptr + (int64_t)par * peer.staging.bytes;
+        p.unpack_base[oi] = ctx->staging + (int64_t)par * ctx->staging_half;
+        p.remote_flag[oi] = reinterpret_cast<unsigned long long*>(peer.ctrl.ptr) + (size_t)opposite_index(oi) * kFlagStrideU64;
+    }
+    order_after_previous(ctx, stream);
+    rc = launch_halo_kernel(p, plan->grid, stream);
+    if (rc) return rc;
+    remember_launch(ctx, stream);
+    if (!(flags & IGG_ASYNC)) {
+        CU(cudaStreamSynchronize(stream));
+        return check_status(ctx);
+    }
+    return IGG_OK;
+}
+
+// gather! -- ref: src/gather.jl:25-54.  Every rank stores its block straight into root's device image of A_global
+// through a CUDA-IPC peer mapping (3-D strided stores, contiguous x-rows); root then hands the image to the caller's
+// array (device-to-device or device-to-host).
+int igg_gather(igg_ctx* ctx, const void* A, const int64_t sizeA_in[3], int ndimsA, void* A_global,
+               const int64_t sizeG_in[3], int ndimsG, int elsize, int root, void* stream_v) {
+    if (!ctx || !A || !sizeA_in) return fail(IGG_ERR_ARG, "igg_gather: NULL argument.");
+    if (!ctx->bootstrapped) return fail(IGG_ERR_STATE, "igg_gather: call igg_bootstrap_import first (nprocs > 1).");
+    if (root < 0 || root >= ctx->g.nprocs) return fail(IGG_ERR_ARG, "igg_gather: invalid root %d.", root);
+    if (elsize < 1 || ndimsA < 1 || ndimsA > 3) return fail(IGG_ERR_ARG, "igg_gather: invalid elsize / ndims.");
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_v);
+    CU(cudaSetDevice(ctx->device));
+    const igg_grid_desc& g = ctx->g;
+    const bool is_root = (g.me == root);
+    int64_t sizeA[3] = {1, 1, 1};
+    for (int d = 0; d < ndimsA; ++d) sizeA[d] = sizeA_in[d];
+    const int64_t bytesA = sizeA[0] * sizeA[1] * sizeA[2] * elsize;
+
+    // Root validates (ref: src/gather.jl:27-33) and tells everyone the verdict, so that no rank hangs.
+    int status = 0;
+    char msg[kMailPayload - 96] = {0};
+    int64_t sizeG[3] = {1, 1, 1};
+    if (is_root) {
+        if (!A_global) { status = IGG_ERR_ARG; snprintf(msg, sizeof(msg), "The input argument `A_global` can't be `nothing` on the root."); }
+        else if (!sizeG_in || ndimsG < 1) { status = IGG_ERR_ARG; snprintf(msg, sizeof(msg), "igg_gather: sizeG missing on root."); }
+        else if (ndimsA > ndimsG) { status = IGG_ERR_ARG; snprintf(msg, sizeof(msg), "The number of dimension of `A` must be less than or equal to the number of dimensions of `A_global`."); }
+        else if (ndimsG > 3) { status = IGG_ERR_ARG; snprintf(msg, sizeof(msg), "The number of dimensions of `A_global` must be less than or equal to the number of dimensions of the Cartesian grid of MPI processes."); }
+        else {
+            for (int d = 0; d < ndimsG; ++d) sizeG[d] = sizeG_in[d];
+            for (int d = 0; d < 3; ++d) {
+                const int64_t want = (d < ndimsG ? g.dims[d] : 1) * sizeA[d];
+                if (d < ndimsG ? sizeG[d] != want : false) status = IGG_ERR_ARG;
+            }
+            // ranks beyond ndimsG dimensions would overwrite each other, the reference requires dims[1:N] only; blocks of
+            // ranks with a non-zero coordinate in a dimension >= ndimsG land on the same place (as with MPI displacements).
+            if (status) snprintf(msg, sizeof(msg), "The size of the global array `size(A_global)` must be equal to the product of `size(A)` and `dims`.");
+            for (int d = ndimsG; d < 3 && !status; ++d)
+                if (g.dims[d] > 1) { status = IGG_ERR_ARG; snprintf(msg, sizeof(msg), "gather!: the process grid has more than one rank in a dimension beyond ndims(A_global)."); }
+        }
+    }
+
+    const int64_t bytesG = sizeG[0] * sizeG[1] * sizeG[2] * elsize;
+    if (g.nprocs == 1) {
+        if (status) return fail(status, "%s", msg);
+        CU(cudaMemcpyAsync(A_global, A, (size_t)bytesA, cudaMemcpyDefault, stream));
+        CU(cudaStreamSynchronize(stream));
+        return IGG_OK;
+    }
+
+    // Round 1 of the hand-shake: root's verdict and whether its device image of A_global must grow.
+    const bool regrow_mine = is_root && !status && bytesG > ctx->gather_bytes;
+    std::vector<SegPayload> all;
+    int rc;
+    {
+        const int64_t keep = ctx->gather_bytes;
+        rc = exchange_segment(ctx, 1, regrow_mine ? -1 : keep, status, msg, all);
+        if (rc) return rc;
+    }
+    if (all[root].status) return fail(all[root].status, "%s", all[root].msg[0] ? all[root].msg : "gather!: root reported an error.");
+    if (all[root].bytes < 0) {
+        // Root replaces its buffer: peers drop the old mapping first, then root reallocates and publishes the new one.
+        if (!is_root) close_segment(ctx->peers[root].gather);
+        rc = ctx->cp.barrier();
+        if (rc) return rc;
+        if (is_root) {
+            CU(cudaDeviceSynchronize());
+            if (ctx->gather_buf) { CU(cudaFree(ctx->gather_buf)); ctx->gather_buf = nullptr; }
+            CU(cudaMalloc(&ctx->gather_buf, (size_t)bytesG));
+            ctx->gather_bytes = bytesG;
+        }
+        rc = exchange_segment(ctx, 1, ctx->gather_bytes, 0, nullptr, all);
+        if (rc) return rc;
+    }
+    const SegPayload& rp = all[root];
+    char* dst_base = nullptr;
+    if (is_root) {
+        dst_base = ctx->gather_buf;
+    } else {
+        Peer& pr = ctx->peers[root];
+        if (pr.gather.ptr && pr.gather.raw != rp.ptr) close_segment(pr.gather);
+        if (!pr.gather.ptr) {
+            rc = open_segment(ctx, pr, rp.handle, rp.ptr, pr.gather);
+            if (rc) return rc;
+            pr.gather.bytes = rp.bytes;
+            pr.gather.raw = rp.ptr;
+        }
+        dst_base = pr.gather.ptr;
+    }
+
+    // Source block: device memory as is, host memory through a device staging copy.
+    const char* src = nullptr;
+    {
+        cudaPointerAttributes a;
+        cudaError_t e = cudaPointerGetAttributes(&a, A);
+        if (e != cudaSuccess) { cudaGetLastError(); return fail(IGG_ERR_CUDA, "cudaPointerGetAttributes failed: %s", cudaGetErrorString(e)); }
+        if (a.type == cudaMemoryTypeDevice || a.type == cudaMemoryTypeManaged) {
+            src = static_cast<const char*>(A);
+        } else {
+            if (bytesA > ctx->gather_src_bytes) {
+                CU(cudaDeviceSynchronize());
+                if (ctx->gather_src) { CU(cudaFree(ctx->gather_src)); ctx->gather_src = nullptr; }
+                CU(cudaMalloc(&ctx->gather_src, (size_t)bytesA));
+                ctx->gather_src_bytes = bytesA;
+            }
+            CU(cudaMemcpyAsync(ctx->gather_src, A, (size_t)bytesA, cudaMemcpyHostToDevice, stream));
+            src = ctx->gather_src;
+        }
+    }
+
+    // Global sizes are known to every rank from dims and sizeA (ref: src/gather.jl:33).
+    int64_t gsz[2] = {sizeA[0] * g.dims[0], sizeA[1] * g.dims[1]};
+    int64_t origin[3] = {g.coords[0] * sizeA[0], g.coords[1] * sizeA[1], g.coords[2] * sizeA[2]};
+    std::vector<TileRec> tiles;
+    build_block_copy_tiles(elsize, sizeA, gsz, origin, (int64_t)((uintptr_t)src % 16), 0, tiles);
+    if ((int)tiles.size() > ctx->gather_tiles_cap) {
+        CU(cudaDeviceSynchronize());
+        if (ctx->d_gather_tiles) CU(cudaFree(ctx->d_gather_tiles));
+        CU(cudaMalloc(&ctx->d_gather_tiles, tiles.size() * sizeof(TileRec)));
+        ctx->gather_tiles_cap = (int)tiles.size();
+    }
+    CU(cudaMemcpyAsync(ctx->d_gather_tiles, tiles.data(), tiles.size() * sizeof(TileRec), cudaMemcpyHostToDevice, stream));
+    KParams p;
+    std::memset(&p, 0, sizeof(p));
+    p.tiles = ctx->d_gather_tiles;
+    p.n_tiles = (int32_t)tiles.size();
+    p.n_push_tiles = 0;
+    p.field[0] = const_cast<char*>(src);
+    p.push_base[0] = dst_base;
+    p.local_flag = reinterpret_cast<const unsigned long long*>(ctx->ctrl);
+    p.push_count = reinterpret_cast<unsigned int*>(ctx->ctrl + kCountersOff);
+    p.status = ctx->d_status;
+    p.timeout_ns = ctx->timeout_ns;
+    order_after_previous(ctx, stream);
+    rc = launch_halo_kernel(p, (int)std::min<int64_t>((int64_t)tiles.size(), (int64_t)ctx->max_blocks * 4), stream);
+    if (rc) return rc;
+    remember_launch(ctx, stream);
+    CU(cudaStreamSynchronize(stream));       // my block has landed in root's memory
+    rc = ctx->cp.barrier();                  // ... and so has everyone else's
+    if (rc) return rc;
+    if (is_root) {
+        CU(cudaMemcpyAsync(A_global, ctx->gather_buf, (size_t)bytesG, cudaMemcpyDefault, stream));
+        CU(cudaStreamSynchronize(stream));
+    }
+    return ctx->cp.barrier();                // root's image may be overwritten by the next gather only after this
+}
+
+int64_t igg_launch_count(const igg_ctx* ctx) { return ctx ? ctx->launches : 0; }
+const char* igg_kernel_name(void) { return halo_kernel_name(); }
+
+}  // extern "C"

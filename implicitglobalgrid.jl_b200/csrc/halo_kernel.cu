@@ -1,0 +1,211 @@
+// The fused halo-exchange kernel of libigg_b200 (sm_100a).
+//
+// One launch per update_halo call does, for all fields and all 26 neighbour offsets:
+//   PUSH   pack a send box of my field and store it straight into the neighbour GPU's staging slot through its
+//          CUDA-IPC peer mapping (NVLink); when the last tile for a neighbour is done, publish an epoch in the
+//          neighbour's arrival flag (st.release.sys).
+//   LOCAL  periodic wrap inside my own array (the rank is its own neighbour): send box -> opposite receive box.
+//   UNPACK wait for the neighbour's epoch (ld.acquire.sys), then copy its staged box into my receive box.
+// It replaces the reference's write_d2x! / read_x2d! kernels, the cuMemcpy3DAsync staging copies, the D2D
+// self-copy and the 12 host-blocking stream synchronisations per field
+// (ref: src/CUDAExt/update_halo.jl:153-259, src/update_halo.jl:51-88).
+//
+// Work is cut into tiles (TileRec, built on the host in plan.cpp); block b handles tiles b, b+grid, ...  Tiles are
+// ordered PUSH, LOCAL, UNPACK, so every block finishes (and signals) its pushes before it may spin on a flag.
+// The grid never exceeds the number of co-resident blocks, so spinning blocks cannot starve pushing ones.
+//
+// Pure data movement: bytes are copied as opaque 1/2/4/8/16-byte words, so results are bit-exact for any element
+// type.  No tensor cores, no shared-memory staging: each tile row is a contiguous run in both source and
+// destination, and strided x-faces degenerate to one element per row (inherent 32-byte-sector granularity).
+#include <cuda_runtime.h>
+
+#include "igg_internal.h"
+
+namespace igg {
+
+namespace {
+
+template <typename V> struct Word;
+
+__device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long long* p) {
+    unsigned long long v;
+    asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+
+__device__ __forceinline__ void st_release_sys(unsigned long long* p, unsigned long long v) {
+    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+
+__device__ __forceinline__ unsigned long long globaltimer_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    return t;
+}
+
+// Loads.  Field data was written by earlier kernels of this stream: default caching, no L1 allocation (streamed
+// once).  Staging data is written by a peer GPU during this kernel: read it at L2 (ld.cg), the point of coherence.
+template <typename V> __device__ __forceinline__ V load_stream(const V* p) { return __ldcs(p); }
+template <typename V> __device__ __forceinline__ V load_l2(const V* p) { return __ldcg(p); }
+template <> __device__ __forceinline__ unsigned char load_stream(const unsigned char* p) { return *p; }
+template <> __device__ __forceinline__ unsigned char load_l2(const unsigned char* p) {
+    return *reinterpret_cast<const volatile unsigned char*>(p);
+}
+template <> __device__ __forceinline__ unsigned short load_stream(const unsigned short* p) { return *p; }
+template <> __device__ __forceinline__ unsigned short load_l2(const unsigned short* p) {
+    return *reinterpret_cast<const volatile unsigned short*>(p);
+}
+
+// Loads kept in flight per thread (more spills registers at 4 blocks per SM).
+template <typename V> struct Unroll { static constexpr int value = 2; };
+
+__device__ __forceinline__ int64_t i64(unsigned lo, unsigned hi) { return (int64_t)(((unsigned long long)hi << 32) | lo); }
+
+// Reads a TileRec with five 16-byte read-only loads and rebuilds it field by field, so that it stays in registers.
+__device__ __forceinline__ TileRec load_tile(const TileRec* g) {
+    const uint4* q = reinterpret_cast<const uint4*>(g);
+    const uint4 a = __ldg(q), b = __ldg(q + 1), c = __ldg(q + 2), d = __ldg(q + 3), e = __ldg(q + 4);
+    TileRec t;
+    t.src_off = i64(a.x, a.y); t.dst_off = i64(a.z, a.w);
+    t.src_sy = i64(b.x, b.y);  t.src_sz = i64(b.z, b.w);
+    t.dst_sy = i64(c.x, c.y);  t.dst_sz = i64(c.z, c.w);
+    t.row0 = d.x; t.nrows = d.y; t.ncols = d.z; t.ny = d.w;
+    t.field = (uint16_t)(e.x & 0xffffu);
+    t.vec_log2 = (uint8_t)((e.x >> 16) & 0xffu);
+    t.kind = (uint8_t)(e.x >> 24);
+    t.nbr = (uint8_t)(e.y & 0xffu);
+    return t;
+}
+
+// Byte offsets of item i of a tile: i -> (row r = i / ncols, column c = i % ncols) -> (y, z) of the flattened row.
+template <typename V>
+__device__ __forceinline__ void item_offsets(const TileRec& t, uint32_t i, int64_t& soff, int64_t& doff) {
+    uint32_t r = 0, c = i;
+    if (t.nrows != 1) { r = i / t.ncols; c = i - r * t.ncols; }
+    const uint32_t row = t.row0 + r;
+    uint32_t z = 0, y = row;
+    if (row >= t.ny) { z = row / t.ny; y = row - z * t.ny; }
+    const int64_t col = (int64_t)c * (int64_t)sizeof(V);
+    soff = (int64_t)y * t.src_sy + (int64_t)z * t.src_sz + col;
+    doff = (int64_t)y * t.dst_sy + (int64_t)z * t.dst_sz + col;
+}
+
+// Copies one tile; all loads of an unrolled group are issued before the first store (offsets are recomputed for
+// the stores instead of being kept live, which keeps the kernel within 64 registers = 4 blocks per SM).
+template <typename V, bool FROM_STAGING>
+__device__ __forceinline__ void copy_tile(const TileRec& t, const char* __restrict__ src, char* __restrict__ dst) {
+    constexpr int kUnroll = Unroll<V>::value;
+    const uint32_t items = t.ncols * t.nrows;
+    for (uint32_t base = threadIdx.x; base < items; base += kThreads * kUnroll) {
+        V v[kUnroll];
+#pragma unroll
+        for (int u = 0; u < kUnroll; ++u) {
+            const uint32_t i = base + u * kThreads;
+            if (i < items) {
+                int64_t soff, doff;
+                item_offsets<V>(t, i, soff, doff);
+                const V* sp = reinterpret_cast<const V*>(src + soff);
+                v[u] = FROM_STAGING ? load_l2<V>(sp) : load_stream<V>(sp);
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < kUnroll; ++u) {
+            const uint32_t i = base + u * kThreads;
+            if (i < items) {
+                int64_t soff, doff;
+                item_offsets<V>(t, i, soff, doff);
+                *reinterpret_cast<V*>(dst + doff) = v[u];
+            }
+        }
+    }
+}
+
+template <bool FROM_STAGING>
+__device__ __forceinline__ void copy_tile_dispatch(const TileRec& t, const char* src, char* dst) {
+    switch (t.vec_log2) {
+        case 4: copy_tile<uint4, FROM_STAGING>(t, src, dst); break;
+        case 3: copy_tile<uint2, FROM_STAGING>(t, src, dst); break;
+        case 2: copy_tile<unsigned int, FROM_STAGING>(t, src, dst); break;
+        case 1: copy_tile<unsigned short, FROM_STAGING>(t, src, dst); break;
+        default: copy_tile<unsigned char, FROM_STAGING>(t, src, dst); break;
+    }
+}
+
+__global__ void __launch_bounds__(kThreads, 4) igg_halo_exchange_kernel(const __grid_constant__ KParams p) {
+    __shared__ unsigned int s_contrib[IGG_NOFFSETS];   // push tiles this block finished, per neighbour offset
+    if (threadIdx.x < IGG_NOFFSETS) s_contrib[threadIdx.x] = 0;
+    __syncthreads();
+    unsigned int arrived = 0;   // (thread 0 only) bit o: neighbour o's epoch has been observed by this block
+
+    bool signalled = (int)blockIdx.x >= p.n_push_tiles;   // blocks without push tiles have nothing to signal
+
+    auto signal = [&]() {
+        // All data stores of this block -> visible system-wide before the counter / flag updates.
+        __syncthreads();
+        if (threadIdx.x < IGG_NOFFSETS) {
+            const unsigned int mine = s_contrib[threadIdx.x];
+            if (mine) {
+                __threadfence_system();
+                const unsigned int old = atomicAdd(p.push_count + threadIdx.x, mine);
+                if (old + mine == p.expected[threadIdx.x]) {      // last block for this neighbour
+                    p.push_count[threadIdx.x] = 0;                // ready for the next call (stream ordered)
+                    __threadfence_system();
+                    st_release_sys(p.remote_flag[threadIdx.x], p.epoch[threadIdx.x]);
+                }
+            }
+        }
+    };
+
+    for (int ti = blockIdx.x; ti < p.n_tiles; ti += gridDim.x) {
+        if (!signalled && ti >= p.n_push_tiles) { signal(); signalled = true; }
+
+        // Tile record: uniform across the block, five 16-byte read-only loads.
+        const TileRec t = load_tile(p.tiles + ti);
+
+        if (t.kind == IGG_OP_UNPACK) {
+            if (threadIdx.x == 0 && !((arrived >> t.nbr) & 1u)) {
+                const unsigned long long* flag = p.local_flag + (size_t)t.nbr * kFlagStrideU64;
+                const unsigned long long want = p.epoch[t.nbr];
+                unsigned long long t0 = 0;
+                unsigned int spins = 0;
+                while (ld_acquire_sys(flag) < want) {
+                    if ((++spins & 0x3ff) == 0) {
+                        const unsigned long long now = globaltimer_ns();
+                        if (t0 == 0) t0 = now;
+                        else if (now - t0 > p.timeout_ns) { *reinterpret_cast<volatile int*>(p.status) = IGG_ERR_TIMEOUT; break; }
+                    }
+                }
+                arrived |= 1u << t.nbr;
+            }
+            __syncthreads();
+            copy_tile_dispatch<true>(t, p.unpack_base[t.nbr] + t.src_off, static_cast<char*>(p.field[t.field]) + t.dst_off);
+        } else {
+            // PUSH: my field -> peer staging; LOCAL: my field -> my field; COPY (gather!): block -> peer array.
+            const char* src = static_cast<const char*>(p.field[t.field]) + t.src_off;
+            char* dst = (t.kind == IGG_OP_LOCAL ? static_cast<char*>(p.field[t.field]) : p.push_base[t.nbr]) + t.dst_off;
+            copy_tile_dispatch<false>(t, src, dst);
+            if (t.kind == IGG_OP_PUSH && threadIdx.x == 0) s_contrib[t.nbr] += 1;
+        }
+    }
+    if (!signalled) signal();
+}
+
+}  // namespace
+
+int halo_kernel_max_coresident_blocks(int device) {
+    int per_sm = 0, sms = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, igg_halo_exchange_kernel, kThreads, 0) != cudaSuccess) return -1;
+    if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device) != cudaSuccess) return -1;
+    return per_sm * sms;
+}
+
+int launch_halo_kernel(const KParams& p, int grid, void* stream) {
+    igg_halo_exchange_kernel<<<grid, kThreads, 0, static_cast<cudaStream_t>(stream)>>>(p);
+    const cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return fail(IGG_ERR_CUDA, "halo kernel launch failed: %s", cudaGetErrorString(e));
+    return IGG_OK;
+}
+
+const char* halo_kernel_name() { return "igg_halo_exchange_kernel"; }
+
+}  // namespace igg

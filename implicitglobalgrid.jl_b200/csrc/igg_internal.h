@@ -1,0 +1,108 @@
+// Internal declarations shared by the host (plan, context) and device (kernel) parts of libigg_b200.
+#pragma once
+
+#include <cstdint>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "igg_b200.h"
+
+namespace igg {
+
+// ---- error reporting ---------------------------------------------------------------------------------------
+void set_error(const char* fmt, ...);          // thread-local message behind igg_last_error()
+int  fail(int code, const char* fmt, ...);     // set_error + return code
+
+// ---- device tables -----------------------------------------------------------------------------------------
+// One tile = the unit of work of one thread block iteration: `nrows` rows starting at flattened row `row0`
+// (row -> (y,z) = (row % ny, row / ny)), each row `ncols` vectors of `1 << vec_log2` bytes.  The column origin is
+// already folded into src_off / dst_off.  80 bytes, read with five 16-byte loads.
+struct alignas(16) TileRec {
+    int64_t  src_off, dst_off;                  // byte offsets from the op's source / destination base pointer
+    int64_t  src_sy, src_sz, dst_sy, dst_sz;    // byte strides between rows (y) and planes (z)
+    uint32_t row0, nrows, ncols, ny;
+    uint16_t field;                             // index into KParams::field
+    uint8_t  vec_log2;                          // 0..4
+    uint8_t  kind;                              // igg_op_kind
+    uint8_t  nbr;                               // neighbour offset index 0..26 (PUSH: target, UNPACK: source)
+    uint8_t  pad[3];
+    uint32_t pad2[2];
+};
+static_assert(sizeof(TileRec) == 80, "TileRec layout");
+
+constexpr int kThreads      = 256;      // threads per block of the halo kernel
+constexpr int kTileBytes    = 8192;     // bytes moved per tile
+constexpr int kFlagStrideU64 = 16;      // one arrival flag per 128-byte line
+
+// Kernel parameters (passed by value, < 4 KB).
+struct KParams {
+    const TileRec* tiles;
+    int32_t  n_tiles;
+    int32_t  n_push_tiles;                     // tiles [0, n_push_tiles) are IGG_OP_PUSH
+    void*    field[IGG_MAX_FIELDS];            // base pointers of the fields of this call
+    char*    push_base[IGG_NOFFSETS];          // peer staging half I write for the neighbour at offset o
+    const char* unpack_base[IGG_NOFFSETS];     // my staging half holding what the neighbour at offset o sent
+    unsigned long long* remote_flag[IGG_NOFFSETS];  // arrival flag in the peer's control segment (its slot -o)
+    const unsigned long long* local_flag;      // my arrival flags, [o * kFlagStrideU64]
+    unsigned int* push_count;                  // my per-offset counters of finished push tiles [27]
+    uint32_t expected[IGG_NOFFSETS];           // push tiles per offset in this plan
+    unsigned long long epoch[IGG_NOFFSETS];    // value to publish / wait for
+    int*     status;                           // host-mapped status word (set on time-out)
+    unsigned long long timeout_ns;
+};
+
+// ---- host-side plan ----------------------------------------------------------------------------------------
+struct FieldKey {
+    int64_t size[3];
+    int64_t hw[3];
+    int32_t elsize;
+    int32_t ndims;
+    int32_t align;       // ptr % 16
+    bool operator==(const FieldKey& o) const { return std::memcmp(this, &o, sizeof(*this)) == 0; }
+};
+
+struct Plan {
+    std::vector<FieldKey>    key;
+    int                      dims_mask = 0;          // bit d set: dimension d (0..2) is updated
+    std::vector<igg_plan_op> ops;                    // PUSH ops, then LOCAL, then UNPACK
+    std::vector<TileRec>     tiles;
+    int32_t  n_push_tiles = 0;
+    uint32_t expected[IGG_NOFFSETS] = {0};
+    uint32_t active_mask = 0;                        // bit o set: this plan exchanges with the neighbour at offset o
+    int32_t  peer[IGG_NOFFSETS];                     // rank at offset o (or -1)
+    int64_t  staging_bytes = 0;                      // bytes of one staging half this plan needs
+    int64_t  bytes_sent = 0;                         // algorithmic halo bytes this rank sends (local + remote)
+    // device copy (owned by the context)
+    TileRec* d_tiles = nullptr;
+    int      grid = 0;
+};
+
+inline int offset_index(const int o[3]) { return (o[0] + 1) + 3 * (o[1] + 1) + 9 * (o[2] + 1); }
+inline void index_offset(int idx, int o[3]) { o[0] = idx % 3 - 1; o[1] = (idx / 3) % 3 - 1; o[2] = idx / 9 - 1; }
+inline int opposite_index(int idx) { return 26 - idx; }
+
+// Validates the grid description (coherent neighbours, disp == 1).
+int check_grid(const igg_grid_desc& g);
+// ol(dim,A) = overlaps[dim] + (size(A,dim) - nxyz[dim])      (ref: src/shared.jl:220)
+inline int64_t field_ol(const igg_grid_desc& g, const igg_field& f, int d) {
+    return g.overlaps[d] + (f.size[d] - g.nxyz[d]);
+}
+int check_fields(const igg_grid_desc& g, int nfields, const igg_field* fields);
+int ranges(const igg_grid_desc& g, const igg_field& f, int n, int dim, bool send, int64_t out[6]);
+// Builds ops + tiles for this rank.  Pure host code.
+int build_plan(const igg_grid_desc& g, int nfields, const igg_field* fields, int dims_mask, Plan& plan);
+void build_block_copy_tiles(int64_t el, const int64_t ext[3], const int64_t dst_size[2], const int64_t dst_origin[3],
+                            int64_t src_align, int64_t dst_align, std::vector<TileRec>& tiles);
+constexpr int kOpCopy = 3;   // internal tile kind: field[t.field] -> push_base[t.nbr], no signalling (gather!)
+// dims=(...) keyword -> bit mask of updated dimensions (NULL / empty = all three).
+int dims_mask_from_order(const int* dims_order, int n, int* mask_out);
+const char* last_error_cstr();
+
+// ---- kernel launcher (halo_kernel.cu) ----------------------------------------------------------------------
+int  halo_kernel_max_coresident_blocks(int device);     // occupancy * SM count
+int  launch_halo_kernel(const KParams& p, int grid, void* stream);
+const char* halo_kernel_name();
+
+}  // namespace igg

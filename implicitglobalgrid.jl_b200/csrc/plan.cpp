@@ -1,0 +1,470 @@
+// Host-side exchange plan: which boxes of which field go where.  Pure C++ (no CUDA calls), so it can be
+// exercised on a machine without a GPU through igg_plan_describe / igg_sendranges / igg_check_fields.
+//
+// Semantics follow the reference (paths relative to the reference root):
+//   - per-field overlap and "has a halo" predicate      src/shared.jl:220, src/update_halo.jl:239,266,346,359,371
+//   - send / receive boxes                              src/update_halo.jl:281-302
+//   - who talks to whom                                 src/update_halo.jl:51-88 (+ MPI Cart_shift, src/create_global_grid.jl:98-100)
+//   - argument checks                                   src/update_halo.jl:418-480
+// The reference runs three dependent phases (z, x, y), each moving full faces.  Here all dimensions are exchanged
+// in ONE phase with up to 26 neighbours: a face message excludes the cells that belong to another updated
+// dimension's halo, and those cells arrive directly from the edge / corner neighbour instead.  Sources are never
+// halo cells and destinations are always halo cells, so the exchange is hazard-free in place and bit-identical to
+// the sequential scheme (checked against the oracle in tests/test_plan_vs_oracle.py).
+#include <algorithm>
+#include <array>
+#include <cstdarg>
+
+#include "igg_internal.h"
+
+namespace igg {
+
+static thread_local std::string g_last_error;
+
+void set_error(const char* fmt, ...) {
+    char buf[1024];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof(buf), fmt, ap);
+    va_end(ap);
+    g_last_error = buf;
+}
+
+int fail(int code, const char* fmt, ...) {
+    char buf[1024];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof(buf), fmt, ap);
+    va_end(ap);
+    g_last_error = buf;
+    return code;
+}
+
+const char* last_error_cstr() { return g_last_error.c_str(); }
+
+static int64_t cart_rank(const int64_t c[3], const int64_t dims[3]) {
+    return (c[0] * dims[1] + c[1]) * dims[2] + c[2];   // row-major (ref: src/gather.jl:40-46)
+}
+
+int check_grid(const igg_grid_desc& g) {
+    int64_t np = 1;
+    for (int d = 0; d < 3; ++d) {
+        if (g.dims[d] < 1) return fail(IGG_ERR_GRID, "Invalid grid: dims[%d] = %lld < 1.", d, (long long)g.dims[d]);
+        if (g.coords[d] < 0 || g.coords[d] >= g.dims[d])
+            return fail(IGG_ERR_GRID, "Invalid grid: coords[%d] out of range.", d);
+        if (g.nxyz[d] < 1) return fail(IGG_ERR_GRID, "Invalid arguments: nx, ny, and nz cannot be less than 1.");
+        if (g.halowidths[d] < 1) return fail(IGG_ERR_GRID, "Invalid arguments: halowidths cannot be less than 1.");
+        if (g.periods[d] != 0 && g.periods[d] != 1)
+            return fail(IGG_ERR_GRID, "Invalid arguments: periodx, periody, and periodz must be either 0 or 1.");
+        np *= g.dims[d];
+    }
+    if (np != g.nprocs) return fail(IGG_ERR_GRID, "Invalid grid: prod(dims) != nprocs.");
+    if (cart_rank(g.coords, g.dims) != g.me)
+        return fail(IGG_ERR_GRID, "Invalid grid: `me` is not the row-major Cartesian rank of `coords`.");
+    for (int d = 0; d < 3; ++d) {
+        const int64_t l = g.neighbors[d][0], r = g.neighbors[d][1];
+        // ref: src/update_halo.jl:57,68,76
+        const bool none_me = (l != g.me) && (r != g.me);
+        const bool all_me = (l == g.me) && (r == g.me);
+        if (!none_me && !all_me)
+            return fail(IGG_ERR_GRID,
+                        "Incoherent neighbors in dimension %d: either all neighbors must equal to me, or none.", d + 1);
+        for (int s = 0; s < 2; ++s) {
+            int64_t c[3] = {g.coords[0], g.coords[1], g.coords[2]};
+            c[d] += s ? 1 : -1;
+            int64_t want;
+            if (g.periods[d]) {
+                c[d] = (c[d] + g.dims[d]) % g.dims[d];
+                want = cart_rank(c, g.dims);
+            } else {
+                want = (c[d] >= 0 && c[d] < g.dims[d]) ? cart_rank(c, g.dims) : IGG_PROC_NULL;
+            }
+            const int64_t got = g.neighbors[d][s] < 0 ? IGG_PROC_NULL : g.neighbors[d][s];
+            if (got != want)
+                return fail(IGG_ERR_UNSUPPORTED,
+                            "neighbors[%d][%d] = %lld is not the rank at coords%+d (%lld): only disp=1 Cartesian "
+                            "topologies are supported.", d, s, (long long)got, s ? 1 : -1, (long long)want);
+        }
+    }
+    return IGG_OK;
+}
+
+static std::string join_positions(const std::vector<std::string>& v) {
+    std::string s;
+    for (size_t i = 0; i < v.size(); ++i) {
+        if (i > 0) s += (i + 1 == v.size()) ? " and " : ", ";
+        s += v[i];
+    }
+    return s;
+}
+
+// ref: src/update_halo.jl:418-480 (the checks that need Julia type information -- isbits, contiguity, array type --
+// stay in the host-language wrapper).
+int check_fields(const igg_grid_desc& g, int nfields, const igg_field* f) {
+    if (nfields < 1) return fail(IGG_ERR_ARG, "update_halo needs at least one field.");
+    if (nfields > IGG_MAX_FIELDS)
+        return fail(IGG_ERR_ARG, "At most %d fields per call are supported (got %d).", IGG_MAX_FIELDS, nfields);
+    for (int i = 0; i < nfields; ++i) {
+        if (!f[i].ptr) return fail(IGG_ERR_ARG, "The field at position %d has a NULL pointer.", i + 1);
+        if (f[i].ndims < 1 || f[i].ndims > 3) return fail(IGG_ERR_ARG, "The field at position %d has ndims outside 1..3.", i + 1);
+        if (f[i].elsize < 1) return fail(IGG_ERR_ARG, "The field at position %d has elsize < 1.", i + 1);
+        for (int d = 0; d < 3; ++d) {
+            if (f[i].size[d] < 1) return fail(IGG_ERR_ARG, "The field at position %d has a size < 1.", i + 1);
+            if (d >= f[i].ndims && f[i].size[d] != 1)
+                return fail(IGG_ERR_ARG, "The field at position %d has size != 1 beyond its ndims.", i + 1);
+        }
+    }
+    std::vector<std::string> pos;
+    for (int i = 0; i < nfields; ++i)
+        for (int d = 0; d < f[i].ndims; ++d)
+            if (f[i].halowidths[d] < 1) { pos.push_back(std::to_string(i + 1)); break; }
+    if (pos.size() > 1) return fail(IGG_ERR_FIELDS, "The fields at positions %s have a halowidth less than 1.", join_positions(pos).c_str());
+    if (pos.size() == 1) return fail(IGG_ERR_FIELDS, "The field at position %s has a halowidth less than 1.", pos[0].c_str());
+
+    pos.clear();
+    for (int i = 0; i < nfields; ++i) {
+        bool none = true;
+        for (int d = 0; d < f[i].ndims; ++d)
+            if (field_ol(g, f[i], d) >= 2 * f[i].halowidths[d]) none = false;
+        if (none) pos.push_back(std::to_string(i + 1));
+    }
+    if (pos.size() > 1) return fail(IGG_ERR_FIELDS, "The fields at positions %s have no halo; remove them from the call.", join_positions(pos).c_str());
+    if (pos.size() == 1) return fail(IGG_ERR_FIELDS, "The field at position %s has no halo; remove it from the call.", pos[0].c_str());
+
+    std::vector<std::pair<int, int>> dup;
+    for (int i = 0; i < nfields; ++i)
+        for (int j = i + 1; j < nfields; ++j)
+            if (f[i].ptr == f[j].ptr) dup.push_back({i + 1, j + 1});
+    if (dup.size() > 2) {
+        pos.clear();
+        for (auto& p : dup) pos.push_back("[" + std::to_string(p.first) + ", " + std::to_string(p.second) + "]");
+        return fail(IGG_ERR_FIELDS, "The pairs of fields with the positions %s are the same; remove any duplicates from the call.", join_positions(pos).c_str());
+    }
+    if (!dup.empty())
+        return fail(IGG_ERR_FIELDS, "The field at position %d is a duplicate of the one at the position %d; remove the duplicate from the call.", dup[0].second, dup[0].first);
+
+    pos.clear();
+    for (int i = 1; i < nfields; ++i)
+        if (f[i].elsize != f[0].elsize || f[i].ndims != f[0].ndims) pos.push_back(std::to_string(i + 1));
+    if (pos.size() > 1) return fail(IGG_ERR_FIELDS, "The fields at positions %s are of different type than the first field; make sure that in a same call all fields are of the same type.", join_positions(pos).c_str());
+    if (pos.size() == 1) return fail(IGG_ERR_FIELDS, "The field at position %s is of different type than the first field; make sure that in a same call all fields are of the same type.", pos[0].c_str());
+    return IGG_OK;
+}
+
+// ref: src/update_halo.jl:281-302.  n = 1|2, dim = 1..3.
+int ranges(const igg_grid_desc& g, const igg_field& f, int n, int dim, bool send, int64_t out[6]) {
+    if (n < 1 || n > 2 || dim < 1 || dim > 3) return fail(IGG_ERR_ARG, "ranges: n must be 1|2 and dim 1..3.");
+    const int d = dim - 1;
+    const int64_t ol = field_ol(g, f, d), hw = f.halowidths[d];
+    if (ol < 2 * hw) return fail(IGG_ERR_FIELDS, "Incoherent arguments: ol(A,dim)<2*halowidths[dim].");
+    int64_t i;
+    if (send) i = (n == 2) ? f.size[d] - (ol - 1) : 1 + (ol - hw);
+    else      i = (n == 2) ? f.size[d] - (hw - 1) : 1;
+    for (int k = 0; k < 3; ++k) { out[2 * k] = 1; out[2 * k + 1] = f.size[k]; }
+    out[2 * d] = i;
+    out[2 * d + 1] = i + hw - 1;
+    return IGG_OK;
+}
+
+namespace {
+
+struct Box { int64_t lo[3], hi[3]; };
+
+int64_t round_up(int64_t v, int64_t a) { return (v + a - 1) / a * a; }
+
+// Merges contiguous dimensions, picks the access width and cuts the copy into tiles.
+// The copy moves `ext[1]*ext[2]` rows of `ext[0]*el` bytes; strides are in bytes.
+struct Lowered { int64_t src_off, dst_off, s_sy, s_sz, d_sy, d_sz, row, ny, nz, v, ntiles, nbytes; };
+
+Lowered emit_tiles(int64_t el, const int64_t ext[3], int64_t src_off, int64_t s_sy, int64_t s_sz, int64_t dst_off,
+                   int64_t d_sy, int64_t d_sz, int64_t src_align, int64_t dst_align, int field_idx, int kind, int nbr,
+                   std::vector<TileRec>& tiles) {
+    int64_t row = ext[0] * el, ny = ext[1], nz = ext[2];
+    if (ny == 1) { ny = nz; nz = 1; s_sy = s_sz; d_sy = d_sz; }
+    while (ny > 1 && s_sy == row && d_sy == row) { row *= ny; ny = nz; nz = 1; s_sy = s_sz; d_sy = d_sz; }
+    if (ny == 1) { s_sy = d_sy = 0; }
+    if (nz == 1) { s_sz = d_sz = 0; }
+    int64_t v = 16;
+    auto bad = [&](int64_t vv) {
+        if (row % vv) return true;
+        if ((src_align + src_off) % vv) return true;
+        if ((dst_align + dst_off) % vv) return true;
+        if (s_sy % vv || s_sz % vv || d_sy % vv || d_sz % vv) return true;
+        return false;
+    };
+    while (v > 1 && bad(v)) v /= 2;
+    int vlog = 0;
+    while ((1 << vlog) < v) ++vlog;
+
+    const int64_t V = row / v, rows = ny * nz;
+    const int64_t per_tile = kTileBytes / v;
+    int64_t S, R;
+    if (V >= per_tile) { S = per_tile; R = 1; } else { S = V; R = std::max<int64_t>(1, per_tile / V); }
+    const int64_t segs = (V + S - 1) / S, rblocks = (rows + R - 1) / R;
+    for (int64_t rb = 0; rb < rblocks; ++rb)
+        for (int64_t sg = 0; sg < segs; ++sg) {
+            TileRec t;
+            std::memset(&t, 0, sizeof(t));
+            t.src_off = src_off + sg * S * v;
+            t.dst_off = dst_off + sg * S * v;
+            t.src_sy = s_sy; t.src_sz = s_sz; t.dst_sy = d_sy; t.dst_sz = d_sz;
+            t.row0 = (uint32_t)(rb * R);
+            t.nrows = (uint32_t)std::min<int64_t>(R, rows - rb * R);
+            t.ncols = (uint32_t)std::min<int64_t>(S, V - sg * S);
+            t.ny = (uint32_t)ny;
+            t.field = (uint16_t)field_idx;
+            t.vec_log2 = (uint8_t)vlog;
+            t.kind = (uint8_t)kind;
+            t.nbr = (uint8_t)nbr;
+            tiles.push_back(t);
+        }
+    return Lowered{src_off, dst_off, s_sy, s_sz, d_sy, d_sz, row, ny, nz, v, segs * rblocks, row * rows};
+}
+
+// Fills the merged low-level form + tiles of one op.  `src_field` / `dst_field`: the box lives in the field array
+// (strides of the field) or in a packed staging slot (strides of the box itself, origin = staging_off).
+void lower_op(const igg_field& f, int field_idx, int kind, int nbr, const Box& sb, const Box& db, bool src_field,
+              bool dst_field, int64_t staging_off, igg_plan_op& op, std::vector<TileRec>& tiles) {
+    const int64_t el = f.elsize;
+    int64_t b[3];
+    for (int d = 0; d < 3; ++d) b[d] = sb.hi[d] - sb.lo[d] + 1;
+    const int64_t fsy = f.size[0] * el, fsz = f.size[0] * f.size[1] * el;
+    const int64_t psy = b[0] * el, psz = b[0] * b[1] * el;
+    auto field_off = [&](const Box& x) { return (x.lo[0] - 1) * el + (x.lo[1] - 1) * fsy + (x.lo[2] - 1) * fsz; };
+    const int64_t align = (int64_t)((uintptr_t)f.ptr % 16);
+    const Lowered L = emit_tiles(el, b, src_field ? field_off(sb) : staging_off, src_field ? fsy : psy,
+                                 src_field ? fsz : psz, dst_field ? field_off(db) : staging_off, dst_field ? fsy : psy,
+                                 dst_field ? fsz : psz, src_field ? align : 0, dst_field ? align : 0, field_idx, kind,
+                                 nbr, tiles);
+    op.src_off = L.src_off; op.dst_off = L.dst_off;
+    op.src_sy = L.s_sy; op.src_sz = L.s_sz; op.dst_sy = L.d_sy; op.dst_sz = L.d_sz;
+    op.row_bytes = L.row; op.ny = L.ny; op.nz = L.nz;
+    op.vec_bytes = (int32_t)L.v;
+    op.ntiles = (int32_t)L.ntiles;
+    op.nbytes = L.nbytes;
+}
+
+}  // namespace
+
+int build_plan(const igg_grid_desc& g, int nfields, const igg_field* fields, int dims_mask, Plan& plan) {
+    int rc = check_grid(g);
+    if (rc) return rc;
+    rc = check_fields(g, nfields, fields);
+    if (rc) return rc;
+
+    plan.key.clear();
+    for (int i = 0; i < nfields; ++i) {
+        FieldKey k;
+        std::memset(&k, 0, sizeof(k));
+        for (int d = 0; d < 3; ++d) { k.size[d] = fields[i].size[d]; k.hw[d] = fields[i].halowidths[d]; }
+        k.elsize = fields[i].elsize; k.ndims = fields[i].ndims;
+        k.align = (int32_t)((uintptr_t)fields[i].ptr % 16);
+        plan.key.push_back(k);
+    }
+    plan.dims_mask = dims_mask;
+    plan.ops.clear();
+    plan.tiles.clear();
+    std::fill(plan.expected, plan.expected + IGG_NOFFSETS, 0u);
+    plan.active_mask = 0;
+    plan.bytes_sent = 0;
+
+    bool exists[3][2];
+    for (int d = 0; d < 3; ++d)
+        for (int s = 0; s < 2; ++s) exists[d][s] = g.neighbors[d][s] >= 0;
+
+    // has-halo predicate per field and dimension (ref: src/shared.jl:220; src/update_halo.jl:239)
+    std::vector<std::array<bool, 3>> halo(nfields);
+    for (int i = 0; i < nfields; ++i)
+        for (int d = 0; d < 3; ++d)
+            halo[i][d] = ((dims_mask >> d) & 1) && field_ol(g, fields[i], d) >= 2 * fields[i].halowidths[d];
+
+    // Staging slots: one per (offset, field), identical on every rank (depends only on field sizes, halowidths and
+    // the updated dimensions, never on which neighbours exist), so a sender can compute the receiver's layout.
+    std::vector<int64_t> slot_off((size_t)IGG_NOFFSETS * nfields, -1);
+    int64_t total = 0;
+    for (int oi = 0; oi < IGG_NOFFSETS; ++oi) {
+        int o[3];
+        index_offset(oi, o);
+        if (!o[0] && !o[1] && !o[2]) continue;
+        plan.peer[oi] = -1;
+        for (int i = 0; i < nfields; ++i) {
+            bool ok = true;
+            int64_t n = fields[i].elsize;
+            for (int d = 0; d < 3; ++d) {
+                if (o[d]) { ok = ok && halo[i][d]; n *= fields[i].halowidths[d]; }
+                else n *= fields[i].size[d];
+            }
+            if (!ok) continue;
+            slot_off[(size_t)oi * nfields + i] = total;
+            total += round_up(n, 128);
+        }
+    }
+    plan.peer[13] = -1;
+    plan.staging_bytes = total;
+
+    std::vector<igg_plan_op> push, local, unpack;
+    std::vector<TileRec> tpush, tlocal, tunpack;
+
+    for (int oi = 0; oi < IGG_NOFFSETS; ++oi) {
+        int o[3];
+        index_offset(oi, o);
+        if (!o[0] && !o[1] && !o[2]) continue;
+        // neighbour at coords + o
+        bool nb_ok = true;
+        int64_t c[3];
+        for (int d = 0; d < 3; ++d) {
+            c[d] = g.coords[d] + o[d];
+            if (o[d]) {
+                nb_ok = nb_ok && exists[d][o[d] > 0 ? 1 : 0];
+                if (g.periods[d]) c[d] = (c[d] + g.dims[d]) % g.dims[d];
+            }
+        }
+        if (!nb_ok) continue;
+        const int64_t peer = cart_rank(c, g.dims);
+        plan.peer[oi] = (int32_t)peer;
+
+        for (int i = 0; i < nfields; ++i) {
+            if (slot_off[(size_t)oi * nfields + i] < 0) continue;
+            const igg_field& f = fields[i];
+            Box snd, rcv_peer, rcv_mine;
+            for (int d = 0; d < 3; ++d) {
+                if (o[d]) {
+                    int64_t r[6];
+                    const int n = o[d] < 0 ? 1 : 2;
+                    ranges(g, f, n, d + 1, true, r);      // my send box of side n ...
+                    snd.lo[d] = r[2 * d]; snd.hi[d] = r[2 * d + 1];
+                    ranges(g, f, 3 - n, d + 1, false, r); // ... lands in the receive box of side 3-n on the peer
+                    rcv_peer.lo[d] = r[2 * d]; rcv_peer.hi[d] = r[2 * d + 1];
+                    ranges(g, f, n, d + 1, false, r);     // what the neighbour at +o sends lands in my side n
+                    rcv_mine.lo[d] = r[2 * d]; rcv_mine.hi[d] = r[2 * d + 1];
+                } else {
+                    // Cells of this dimension's own halo are delivered by the edge / corner neighbours instead.
+                    const int64_t lo = (halo[i][d] && exists[d][0]) ? f.halowidths[d] + 1 : 1;
+                    const int64_t hi = (halo[i][d] && exists[d][1]) ? f.size[d] - f.halowidths[d] : f.size[d];
+                    snd.lo[d] = rcv_peer.lo[d] = rcv_mine.lo[d] = lo;
+                    snd.hi[d] = rcv_peer.hi[d] = rcv_mine.hi[d] = hi;
+                }
+            }
+            bool empty = false;
+            for (int d = 0; d < 3; ++d) empty = empty || snd.hi[d] < snd.lo[d];
+            if (empty) continue;
+
+            igg_plan_op op;
+            std::memset(&op, 0, sizeof(op));
+            op.field = i;
+            for (int d = 0; d < 3; ++d) {
+                op.offset[d] = o[d];
+                op.src_lo[d] = snd.lo[d]; op.src_hi[d] = snd.hi[d];
+                op.dst_lo[d] = rcv_peer.lo[d]; op.dst_hi[d] = rcv_peer.hi[d];
+            }
+            op.peer = (int32_t)peer;
+            if (peer == g.me) {
+                op.kind = IGG_OP_LOCAL;
+                op.staging_off = -1;
+                lower_op(f, i, IGG_OP_LOCAL, oi, snd, rcv_peer, true, true, 0, op, tlocal);
+                local.push_back(op);
+                plan.bytes_sent += op.nbytes;
+            } else {
+                op.kind = IGG_OP_PUSH;
+                op.staging_off = slot_off[(size_t)opposite_index(oi) * nfields + i];
+                lower_op(f, i, IGG_OP_PUSH, oi, snd, snd, true, false, op.staging_off, op, tpush);
+                push.push_back(op);
+                plan.expected[oi] += (uint32_t)op.ntiles;
+                plan.active_mask |= 1u << oi;
+                plan.bytes_sent += op.nbytes;
+
+                igg_plan_op up;
+                std::memset(&up, 0, sizeof(up));
+                up.kind = IGG_OP_UNPACK;
+                up.field = i;
+                up.peer = (int32_t)peer;
+                for (int d = 0; d < 3; ++d) {
+                    up.offset[d] = o[d];
+                    up.dst_lo[d] = rcv_mine.lo[d]; up.dst_hi[d] = rcv_mine.hi[d];
+                    up.src_lo[d] = up.src_hi[d] = 0;
+                }
+                up.staging_off = slot_off[(size_t)oi * nfields + i];
+                lower_op(f, i, IGG_OP_UNPACK, oi, rcv_mine, rcv_mine, false, true, up.staging_off, up, tunpack);
+                unpack.push_back(up);
+            }
+        }
+    }
+
+    plan.n_push_tiles = (int32_t)tpush.size();
+    plan.ops = push;
+    plan.ops.insert(plan.ops.end(), local.begin(), local.end());
+    plan.ops.insert(plan.ops.end(), unpack.begin(), unpack.end());
+    plan.tiles = tpush;
+    plan.tiles.insert(plan.tiles.end(), tlocal.begin(), tlocal.end());
+    plan.tiles.insert(plan.tiles.end(), tunpack.begin(), tunpack.end());
+    return IGG_OK;
+}
+
+// Tiles for copying a dense column-major block of `ext` elements into a box of a larger dense array whose first two
+// extents are `dst_size` (used by gather!, ref: src/gather.jl:36-49, and for dense copies with dst_size == ext).
+void build_block_copy_tiles(int64_t el, const int64_t ext[3], const int64_t dst_size[2], const int64_t dst_origin[3],
+                            int64_t src_align, int64_t dst_align, std::vector<TileRec>& tiles) {
+    const int64_t dsy = dst_size[0] * el, dsz = dst_size[0] * dst_size[1] * el;
+    const int64_t dst_off = dst_origin[0] * el + dst_origin[1] * dsy + dst_origin[2] * dsz;
+    emit_tiles(el, ext, 0, ext[0] * el, ext[0] * ext[1] * el, dst_off, dsy, dsz, src_align, dst_align, 0, 3 /*COPY*/, 0, tiles);
+}
+
+}  // namespace igg
+
+// ---- C ABI: host-only helpers --------------------------------------------------------------------------------
+namespace igg { const char* last_error_cstr(); }
+
+extern "C" {
+
+int igg_version(void) { return IGG_VERSION; }
+const char* igg_last_error(void) { return igg::last_error_cstr(); }
+
+int igg_sendranges(const igg_grid_desc* desc, const igg_field* f, int n, int dim, int64_t out[6]) {
+    if (!desc || !f || !out) return igg::fail(IGG_ERR_ARG, "igg_sendranges: NULL argument.");
+    return igg::ranges(*desc, *f, n, dim, true, out);
+}
+
+int igg_recvranges(const igg_grid_desc* desc, const igg_field* f, int n, int dim, int64_t out[6]) {
+    if (!desc || !f || !out) return igg::fail(IGG_ERR_ARG, "igg_recvranges: NULL argument.");
+    return igg::ranges(*desc, *f, n, dim, false, out);
+}
+
+int igg_check_fields(const igg_grid_desc* desc, int nfields, const igg_field* fields) {
+    if (!desc || !fields) return igg::fail(IGG_ERR_ARG, "igg_check_fields: NULL argument.");
+    return igg::check_fields(*desc, nfields, fields);
+}
+
+}  // extern "C"
+
+int igg::dims_mask_from_order(const int* dims_order, int n, int* mask_out) {
+    int mask = 0;
+    if (!dims_order || n <= 0) { *mask_out = 7; return IGG_OK; }   // default dims=(3,1,2): all dimensions
+    for (int i = 0; i < n; ++i) {
+        if (dims_order[i] < 1 || dims_order[i] > 3) return igg::fail(IGG_ERR_ARG, "dims entries must be in 1..3.");
+        mask |= 1 << (dims_order[i] - 1);
+    }
+    *mask_out = mask;
+    return IGG_OK;
+}
+
+extern "C" {
+
+int igg_plan_describe(const igg_grid_desc* desc, int nfields, const igg_field* fields, const int* dims_order,
+                      int ndims_order, igg_plan_op* ops_out, int ops_cap, int* nops_out, int64_t* staging_bytes_out) {
+    if (!desc || !fields || !nops_out) return igg::fail(IGG_ERR_ARG, "igg_plan_describe: NULL argument.");
+    int mask;
+    int rc = igg::dims_mask_from_order(dims_order, ndims_order, &mask);
+    if (rc) return rc;
+    igg::Plan plan;
+    rc = igg::build_plan(*desc, nfields, fields, mask, plan);
+    if (rc) return rc;
+    *nops_out = (int)plan.ops.size();
+    if (staging_bytes_out) *staging_bytes_out = plan.staging_bytes;
+    if (ops_out) {
+        if (ops_cap < (int)plan.ops.size()) return igg::fail(IGG_ERR_ARG, "igg_plan_describe: ops_cap too small (need %d).", (int)plan.ops.size());
+        std::memcpy(ops_out, plan.ops.data(), plan.ops.size() * sizeof(igg_plan_op));
+    }
+    return IGG_OK;
+}
+
+}  // extern "C"

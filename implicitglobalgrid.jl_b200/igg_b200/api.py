@@ -1,0 +1,403 @@
+"""Host-side mirror of the reference API for the halo path, on top of the C ABI of libigg_b200.
+
+Same names, argument meaning and error behaviour as the Julia functions (Julia's `!` becomes a trailing
+underscore-free name: `update_halo`, `gather`):
+
+    init_global_grid   ref: src/init_global_grid.jl:83-113, src/create_global_grid.jl:35-111
+    update_halo        ref: src/update_halo.jl:30-42       (-> igg_update_halo, one C call)
+    gather             ref: src/gather.jl:18-54            (-> igg_gather, one C call)
+    finalize_global_grid  ref: src/finalize_global_grid.jl:15-28
+    select_device      ref: src/select_device.jl:16-39
+    nx_g ... x_g ... ix_g ...  ref: src/tools.jl:47-380
+
+Arrays are `torch` tensors holding a column-major array: a Julia array of size (nx,ny,nz) is a tensor of shape
+(nx,ny,nz) with strides (1,nx,nx*ny) -- `igg_b200.zeros((nx,ny,nz))` makes one.  torch is used for device memory,
+streams and (when there is more than one rank) for the one-time all-gather of the bootstrap blobs; it plays the role
+MPI.jl plays in the Julia host.  All data movement happens in libigg_b200's CUDA kernel.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import time
+from dataclasses import dataclass
+from typing import Optional, Sequence, Tuple
+
+from . import _lib as L
+from . import topology as T
+from .topology import ArgumentError
+
+NDIMS_MPI = 3
+NNEIGHBORS_PER_DIM = 2
+
+
+@dataclass
+class GlobalGrid:
+    """ref: src/shared.jl:58-81."""
+    nxyz_g: Tuple[int, int, int]
+    nxyz: Tuple[int, int, int]
+    dims: Tuple[int, int, int]
+    overlaps: Tuple[int, int, int]
+    halowidths: Tuple[int, int, int]
+    origin: Tuple[float, float, float]
+    origin_on_vertex: bool
+    centerxyz: Tuple[bool, bool, bool]
+    nprocs: int
+    me: int
+    coords: Tuple[int, int, int]
+    neighbors: Tuple[Tuple[int, int, int], Tuple[int, int, int]]   # neighbors[n][dim]
+    periods: Tuple[int, int, int]
+    disp: int
+    reorder: int
+    comm: object
+    cuda_enabled: bool
+    quiet: bool
+    device_id: int = 0
+    ctx: Optional[int] = None           # igg_ctx*
+    desc: Optional[L.GridDesc] = None
+
+
+_grid: Optional[GlobalGrid] = None
+_t0 = 0.0
+
+
+def _torch():
+    import torch
+    return torch
+
+
+def grid_is_initialized() -> bool:
+    return _grid is not None
+
+
+def check_initialized():
+    if _grid is None:
+        raise ArgumentError("No function of the module can be called before init_global_grid().")
+
+
+def global_grid() -> GlobalGrid:
+    if _grid is None:
+        raise ArgumentError("No global grid has been created and activated yet, or the package has not been initialized.")
+    return _grid
+
+
+def get_global_grid() -> GlobalGrid:
+    check_initialized()
+    import copy
+    g = copy.copy(_grid)
+    g.ctx = None
+    return g
+
+
+class _Comm:
+    """What `comm` is in this harness: the torch.distributed world (or a single process)."""
+
+    def __init__(self, rank, size):
+        self.rank, self.size = rank, size
+
+    def allgather_bytes(self, b: bytes):
+        if self.size == 1:
+            return [b]
+        dist = _torch().distributed
+        out = [None] * self.size
+        dist.all_gather_object(out, b)
+        return out
+
+    def barrier(self):
+        if self.size > 1:
+            _torch().distributed.barrier()
+
+
+def _world():
+    torch = _torch()
+    if torch.distributed.is_available() and torch.distributed.is_initialized():
+        return torch.distributed.get_rank(), torch.distributed.get_world_size()
+    return 0, 1
+
+
+def select_device(gg: Optional[GlobalGrid] = None) -> int:
+    """Device = node-local rank (ref: src/select_device.jl:28-35)."""
+    torch = _torch()
+    g = gg or global_grid()
+    if not g.cuda_enabled:
+        raise ArgumentError("Cannot select a device because neither CUDA nor AMDGPU is enabled (meaning that the "
+                            "corresponding module was not imported before ImplicitGlobalGrid).")
+    me_l = int(os.environ.get("LOCAL_RANK", g.me))
+    nl = int(os.environ.get("LOCAL_WORLD_SIZE", g.nprocs))
+    if nl > torch.cuda.device_count():
+        raise ArgumentError("More processes have been launched per node than there are GPUs available.")
+    torch.cuda.set_device(me_l)
+    return me_l
+
+
+def init_global_grid(nx, ny=1, nz=1, *, dimx=0, dimy=0, dimz=0, periodx=0, periody=0, periodz=0,
+                     origin=(0.0, 0.0, 0.0), origin_on_vertex=False, centerx=False, centery=False, centerz=False,
+                     overlaps=(2, 2, 2), halowidths=None, disp=1, reorder=1, comm=None, init_MPI=True,
+                     device_type="auto", select_device=True, quiet=False):
+    """Returns (me, dims, nprocs, coords, comm) like the reference."""
+    global _grid
+    if _grid is not None:
+        raise ArgumentError("init_global_grid() can only be called once before finalize_global_grid().")
+    if device_type not in ("none", "auto", "CUDA", "AMDGPU"):
+        raise ArgumentError(f"Argument `device_type`: invalid value obtained ({device_type}). Valid values are: CUDA, "
+                            "AMDGPU, none, auto")
+    if device_type in ("none", "AMDGPU"):
+        raise ArgumentError("libigg_b200 is a CUDA-only implementation of the halo path: device_type must be \"auto\" "
+                            "or \"CUDA\" (there is no CPU or AMDGPU path).")
+    overlaps = tuple(int(o) for o in overlaps)
+    if halowidths is None:
+        halowidths = tuple(max(1, o // 2) for o in overlaps)
+    halowidths = tuple(int(h) for h in halowidths)
+    nxyz, dims, periods, origin = T.normalize_input(nx, ny, nz, dimx, dimy, dimz, periodx, periody, periodz, origin,
+                                                    origin_on_vertex, centerx, centery, centerz, overlaps, halowidths,
+                                                    disp)
+    torch = _torch()
+    me, nprocs = _world() if comm is None else (comm.rank, comm.size)
+    comm = comm or _Comm(me, nprocs)
+    dims = T.dims_create(nprocs, dims)
+    coords = T.cart_coords(me, dims)
+    left, right = [], []
+    for i in range(NDIMS_MPI):
+        l, r = T.cart_shift(coords, dims, periods, i, disp)
+        left.append(l)
+        right.append(r)
+    nxyz_g = tuple(d * (n - o) + o * (p == 0) for d, n, o, p in zip(dims, nxyz, overlaps, periods))
+    cuda_enabled = torch.cuda.is_available()
+    g = GlobalGrid(nxyz_g, nxyz, dims, overlaps, halowidths, origin, origin_on_vertex, (centerx, centery, centerz),
+                   nprocs, me, coords, (tuple(left), tuple(right)), periods, disp, reorder, comm, cuda_enabled, quiet)
+    if not quiet and me == 0:
+        print(f"Global grid: {nxyz_g[0]}x{nxyz_g[1]}x{nxyz_g[2]} (nprocs: {nprocs}, dims: {dims[0]}x{dims[1]}x{dims[2]}; "
+              f"device support: {'CUDA (libigg_b200, NVLink peer stores)' if cuda_enabled else 'none'})")
+    if not cuda_enabled:
+        raise L.IGGError(L.IGG_ERR_CUDA, "No usable CUDA device; libigg_b200 has no CPU fallback.")
+    g.device_id = globals()["select_device"](g) if select_device else torch.cuda.current_device()
+    # C context + one-time rank bootstrap (replaces the MPI transport of the halo path)
+    lib = L.load()
+    g.desc = L.make_desc(nxyz, dims, coords, g.neighbors, periods, overlaps, halowidths, me, nprocs, g.device_id)
+    ctx = C.c_void_p()
+    L.check(lib.igg_create(C.byref(g.desc), C.byref(ctx)))
+    g.ctx = ctx.value
+    if nprocs > 1:
+        n = lib.igg_bootstrap_size()
+        blob = C.create_string_buffer(n)
+        L.check(lib.igg_bootstrap_export(g.ctx, blob))
+        blobs = comm.allgather_bytes(blob.raw)
+        allb = C.create_string_buffer(b"".join(blobs), n * nprocs)
+        L.check(lib.igg_bootstrap_import(g.ctx, allb, nprocs))
+    _grid = g
+    tic()
+    toc()
+    return g.me, g.dims, g.nprocs, g.coords, g.comm
+
+
+def finalize_global_grid(*, finalize_MPI=True):
+    global _grid
+    check_initialized()
+    if _grid.ctx:
+        L.check(L.load().igg_destroy(_grid.ctx))
+    _grid = None
+
+
+# ---- fields --------------------------------------------------------------------------------------------------
+
+def zeros(shape, dtype=None, device=None, pin_memory=False):
+    """A zero-initialised column-major array of Julia size `shape` as a torch tensor (shape == `shape`)."""
+    torch = _torch()
+    shape = tuple(int(s) for s in (shape if isinstance(shape, (tuple, list)) else (shape,)))
+    dtype = dtype or torch.float64
+    if device is None:
+        device = "cpu" if pin_memory else f"cuda:{torch.cuda.current_device()}"
+    t = torch.zeros(tuple(reversed(shape)), dtype=dtype, device=device, pin_memory=pin_memory)
+    return t.permute(*reversed(range(len(shape))))
+
+
+def from_numpy(a, device=None):
+    """Column-major torch tensor holding the values of numpy array `a` (any memory order), same shape."""
+    torch = _torch()
+    import numpy as np
+    dt = a.dtype
+    view_as = {np.dtype(np.uint16): np.int16, np.dtype(np.uint32): np.int32, np.dtype(np.uint64): np.int64}
+    b = np.ascontiguousarray(a.transpose(tuple(reversed(range(a.ndim)))))
+    if dt in view_as:
+        b = b.view(view_as[dt])
+    t = torch.from_numpy(b)
+    if device is None:
+        device = f"cuda:{torch.cuda.current_device()}"
+    return t.to(device).permute(*reversed(range(a.ndim)))
+
+
+def to_numpy(t, dtype=None):
+    """numpy array (order='F') with the values of column-major tensor `t`; `dtype` reinterprets the bits."""
+    import numpy as np
+    b = t.permute(*reversed(range(t.dim()))).contiguous().cpu().numpy()
+    if dtype is not None:
+        b = b.view(dtype)
+    return np.asfortranarray(b.transpose(tuple(reversed(range(b.ndim)))))
+
+
+def _is_column_major(t) -> bool:
+    exp = 1
+    for s, st in zip(t.shape, t.stride()):
+        if s != 1 and st != exp:
+            return False
+        exp *= s
+    return True
+
+
+def _wrap(A):
+    """extract / wrap_field (ref: src/shared.jl:246-256): tensor | (tensor, halowidths) | {'A':..,'halowidths':..}."""
+    if isinstance(A, dict):
+        return A["A"], tuple(int(h) for h in A["halowidths"])
+    if isinstance(A, (tuple, list)) and len(A) == 2 and not hasattr(A, "shape"):
+        return A[0], tuple(int(h) for h in A[1])
+    return A, tuple(global_grid().halowidths)
+
+
+def _c_fields(fields):
+    out = []
+    for i, (A, hw) in enumerate(fields):
+        if not hasattr(A, "data_ptr"):
+            raise ArgumentError(f"The field at position {i + 1} does not have a supported array type.")
+        if A.dim() < 1 or A.dim() > 3:
+            raise ArgumentError(f"The field at position {i + 1} does not have a supported array type.")
+        if not _is_column_major(A):
+            raise ArgumentError(f"The field at position {i + 1} is non-contiguous (in indexing)..")
+        out.append(L.make_field(A.data_ptr(), tuple(A.shape), hw, A.element_size()))
+    return out
+
+
+def update_halo(*A, dims=(3, 1, 2), stream=None, blocking=True):
+    """update_halo!(A...; dims=(3,1,2))  -- ref: src/update_halo.jl:30-42.
+
+    Extra keywords: `stream` (a torch.cuda.Stream, default: the current stream) and `blocking=False` for a
+    stream-ordered call (the overlap API of SURVEY section 8f); the default blocks like the reference.
+    """
+    check_initialized()
+    g = global_grid()
+    torch = _torch()
+    fields = [_wrap(a) for a in A]
+    # checks that need type information stay on the host side (ref: src/update_halo.jl:465-479)
+    diff = [i + 1 for i in range(1, len(fields))
+            if fields[i][0].dtype != fields[0][0].dtype or fields[i][0].dim() != fields[0][0].dim()
+            or fields[i][0].device.type != fields[0][0].device.type]
+    cf = _c_fields(fields)
+    arr = (L.Field * len(cf))(*cf)
+    lib = L.load()
+    L.check(lib.igg_check_fields(C.byref(g.desc), len(cf), arr))
+    if len(diff) > 1:
+        raise ArgumentError("The fields at positions " + ", ".join(map(str, diff[:-1])) + f" and {diff[-1]} are of "
+                            "different type than the first field; make sure that in a same call all fields are of the "
+                            "same type.")
+    if diff:
+        raise ArgumentError(f"The field at position {diff[0]} is of different type than the first field; make sure that "
+                            "in a same call all fields are of the same type.")
+    d = (C.c_int * len(dims))(*[int(x) for x in dims])
+    s = stream if stream is not None else torch.cuda.current_stream()
+    L.check(lib.igg_update_halo(g.ctx, len(cf), arr, d, len(dims), C.c_void_p(s.cuda_stream),
+                                L.IGG_SYNC if blocking else L.IGG_ASYNC))
+    return None
+
+
+def gather(A, A_global, *, root=0, stream=None):
+    """gather!(A, A_global; root=0)  -- ref: src/gather.jl:18-54.  `A_global` may be None on non-root ranks."""
+    g = global_grid()
+    torch = _torch()
+    lib = L.load()
+    if not _is_column_major(A) or (A_global is not None and not _is_column_major(A_global)):
+        raise ArgumentError("gather!: arrays must be contiguous column-major arrays.")
+    if A_global is not None and A_global.dtype != A.dtype:
+        raise ArgumentError("gather!: `A` and `A_global` must have the same element type.")
+    sA = (C.c_int64 * 3)(*(tuple(A.shape) + (1,) * (3 - A.dim())))
+    if A_global is not None:
+        sG = (C.c_int64 * 3)(*(tuple(A_global.shape) + (1,) * (3 - A_global.dim())))
+        gp, gnd = C.c_void_p(A_global.data_ptr()), A_global.dim()
+    else:
+        sG, gp, gnd = None, None, 0
+    s = stream if stream is not None else torch.cuda.current_stream()
+    L.check(lib.igg_gather(g.ctx, C.c_void_p(A.data_ptr()), sA, A.dim(), gp, sG, gnd, A.element_size(), int(root),
+                           C.c_void_p(s.cuda_stream)))
+    return None
+
+
+# ---- tools (ref: src/tools.jl) ---------------------------------------------------------------------------------
+
+def _size(A, d):
+    shp = tuple(A.shape) if hasattr(A, "shape") else tuple(A)
+    return shp[d] if d < len(shp) else 1
+
+
+def _n_g(d, nA=None):
+    g = global_grid()
+    base = g.nxyz_g[d]
+    if nA is None:
+        return base
+    diff = nA - g.nxyz[d]
+    p = 1 if g.periods[d] else 0
+    return base + diff * (1 - p) + min(diff + g.overlaps[d], 0) * p
+
+
+def nx_g(A=None): return _n_g(0, None if A is None else (A if isinstance(A, int) else _size(A, 0)))
+def ny_g(A=None): return _n_g(1, None if A is None else (A if isinstance(A, int) else _size(A, 1)))
+def nz_g(A=None): return _n_g(2, None if A is None else (A if isinstance(A, int) else _size(A, 2)))
+
+
+def _i_g(d, i, nA, wrap_periodic=True, coord=None):
+    g = global_grid()
+    coord = g.coords[d] if coord is None else coord
+    diff = nA - g.nxyz[d]
+    olA = g.overlaps[d] + diff
+    nga = _n_g(d, nA)
+    i0 = -int(olA / 2) if g.periods[d] else 0
+    ii = coord * (g.nxyz[d] - g.overlaps[d]) + i + i0
+    if g.periods[d] and wrap_periodic:
+        if ii > nga:
+            ii -= nga
+        if ii < 1:
+            ii += nga
+    return ii
+
+
+def ix_g(ix, A, wrap_periodic=True): return _i_g(0, ix, _size(A, 0), wrap_periodic)
+def iy_g(iy, A, wrap_periodic=True): return _i_g(1, iy, _size(A, 1), wrap_periodic)
+def iz_g(iz, A, wrap_periodic=True): return _i_g(2, iz, _size(A, 2), wrap_periodic)
+
+
+def _x_g(d, i, dx, nA, wrap_periodic=True):
+    g = global_grid()
+    ig = _i_g(d, i, nA, wrap_periodic)
+    diff = nA - g.nxyz[d]
+    ng = g.dims[d] * (g.nxyz[d] - g.overlaps[d]) + g.overlaps[d] * (0 if g.periods[d] else 1)
+    l = dx * ng if g.origin_on_vertex else dx * (ng - 1)
+    lA = l + dx * diff
+    x1 = g.origin[d] + (-l * 0.5 if g.centerxyz[d] else 0.0) + dx * (
+        (0.5 if g.origin_on_vertex else 0.0) + (-diff * 0.5 if not g.periods[d] else 0.0)
+        + (-0.5 if (g.periods[d] and diff % 2 != 0) else 0.0))
+    npts = int(lA / dx + 1e-9) + 1
+    if ig > npts:
+        return x1 + (npts - 1) * dx + dx * (ig - npts)
+    if ig < 1:
+        return x1 - dx * (1 - ig)
+    return x1 + (ig - 1) * dx
+
+
+def x_g(ix, dx, A, wrap_periodic=True): return _x_g(0, ix, dx, _size(A, 0), wrap_periodic)
+def y_g(iy, dy, A, wrap_periodic=True): return _x_g(1, iy, dy, _size(A, 1), wrap_periodic)
+def z_g(iz, dz, A, wrap_periodic=True): return _x_g(2, iz, dz, _size(A, 2), wrap_periodic)
+
+
+def tic():
+    """ref: src/tools.jl:892-898 (MPI.Barrier + time())."""
+    global _t0
+    check_initialized()
+    if _grid.cuda_enabled:
+        _torch().cuda.synchronize()
+    _grid.comm.barrier()
+    _t0 = time.time()
+
+
+def toc():
+    check_initialized()
+    if _grid.cuda_enabled:
+        _torch().cuda.synchronize()
+    _grid.comm.barrier()
+    return time.time() - _t0

@@ -1,0 +1,187 @@
+/* igg_b200.h -- C ABI of libigg_b200.so: the B200-native halo-update path of ImplicitGlobalGrid.jl v0.17.1.
+ *
+ * This library replaces, below the reference's `_update_halo!` / `gather!`, everything that moves data:
+ * buffer allocation, pack/unpack kernels, stream handling and the MPI messages.  The host language (Julia via
+ * `ccall`, Python via `ctypes`, C/C++) keeps the reference's API surface (init_global_grid, update_halo!,
+ * gather!, finalize_global_grid, x_g/nx_g ...) and the process topology (MPI.jl Cart_create / Cart_shift or an
+ * equivalent), and hands this library a plain description of the grid and raw device pointers.
+ *
+ * All functions return 0 (IGG_OK) on success and a negative error code otherwise; `igg_last_error()` returns a
+ * thread-local message whose text mirrors the reference's `error("...")` strings where one exists.
+ * The library does not link MPI or NCCL (NCCL is dlopen'ed only by the comparison path).  There is no CPU
+ * fallback: every data-moving entry point fails with IGG_ERR_CUDA if no CUDA device is usable.
+ *
+ * Citations `ref:` are relative to the reference repository root.
+ */
+#ifndef IGG_B200_H
+#define IGG_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define IGG_VERSION 100          /* 0.1.0 */
+#define IGG_PROC_NULL (-1)       /* stand-in for MPI.PROC_NULL in igg_grid_desc.neighbors */
+#define IGG_MAX_FIELDS 32        /* fields per update_halo call */
+#define IGG_NOFFSETS 27          /* neighbour offsets (-1,0,1)^3, index = (ox+1) + 3*(oy+1) + 9*(oz+1) */
+
+enum igg_status {
+    IGG_OK = 0,
+    IGG_ERR_ARG = -1,          /* invalid argument (NULL pointer, bad size ...) */
+    IGG_ERR_CUDA = -2,         /* a CUDA runtime call failed (message has the CUDA error string) */
+    IGG_ERR_STATE = -3,        /* call order violated (e.g. multi-rank update before bootstrap import) */
+    IGG_ERR_FIELDS = -4,       /* check_fields failure; message = reference text (ref: src/update_halo.jl:418-480) */
+    IGG_ERR_IPC = -5,          /* CUDA-IPC / shared-memory control plane failure */
+    IGG_ERR_NCCL = -6,         /* NCCL comparison path failure */
+    IGG_ERR_TIMEOUT = -7,      /* a neighbour did not arrive (device flag or host mailbox) within the time limit */
+    IGG_ERR_UNSUPPORTED = -8,  /* valid in the reference but not supported here (e.g. disp != 1) */
+    IGG_ERR_GRID = -9          /* incoherent grid description (ref: src/update_halo.jl:76, src/shared.jl:156-207) */
+};
+
+enum igg_flags {
+    IGG_SYNC = 0,   /* default: block the host until the halos are written (the reference's semantics,
+                       ref: src/update_halo.jl:82-87) */
+    IGG_ASYNC = 1   /* stream-ordered: return after the launch; completion is ordered on `stream` */
+};
+
+enum igg_mode {
+    IGG_MODE_IPC_1PHASE = 0,  /* default: one fused kernel, all 26 neighbour regions in one phase, peer stores over
+                                 NVLink + device-side flags */
+    IGG_MODE_NCCL_3PHASE = 1  /* comparison path: pack kernel -> grouped ncclSend/ncclRecv -> unpack kernel, one
+                                 phase per dimension in the reference's order (ref: src/update_halo.jl:51-88) */
+};
+
+/* Mirror of the reference's GlobalGrid (ref: src/shared.jl:58-81), reduced to what the halo path reads.
+ * `neighbors[d][s]` is the rank of the neighbour in dimension d (0..2) on side s (0 = left/low, 1 = right/high)
+ * or IGG_PROC_NULL; this is the memory order of the Julia 2x3 matrix `gg.neighbors`, so it can be passed as is.
+ * Ranks must follow the MPI Cartesian convention rank = (cx*dims[1] + cy)*dims[2] + cz (row-major,
+ * ref: src/gather.jl:40-46). */
+typedef struct igg_grid_desc {
+    int64_t nxyz[3];        /* local base grid size                      (gg.nxyz)       */
+    int64_t dims[3];        /* process grid                              (gg.dims)       */
+    int64_t coords[3];      /* my Cartesian coordinates                  (gg.coords)     */
+    int64_t neighbors[3][2];/* see above                                 (gg.neighbors)  */
+    int64_t periods[3];     /* 0/1                                       (gg.periods)    */
+    int64_t overlaps[3];    /*                                           (gg.overlaps)   */
+    int64_t halowidths[3];  /* default halowidths                        (gg.halowidths) */
+    int32_t me;             /* my rank                                   (gg.me)         */
+    int32_t nprocs;         /*                                           (gg.nprocs)     */
+    int32_t device;         /* CUDA device ordinal to use (ref: src/select_device.jl:28-35: node-local rank) */
+    int32_t reserved;       /* must be 0 */
+} igg_grid_desc;
+
+/* One field of an update_halo call = the reference's GGField (A, halowidths) (ref: src/shared.jl:50,252-256).
+ * `ptr` addresses a dense column-major array of `size[0] x size[1] x size[2]` elements of `elsize` bytes
+ * (size[d] = 1 for d >= ndims).  It may be device memory of the context's device, or page-locked host memory
+ * that is mapped into the device address space (then the kernels read/write it over PCIe). */
+typedef struct igg_field {
+    void*   ptr;
+    int64_t size[3];
+    int64_t halowidths[3];
+    int32_t elsize;         /* bytes per element, any value >= 1 (isbits types) */
+    int32_t ndims;          /* 1..3 */
+} igg_field;
+
+typedef struct igg_ctx igg_ctx;
+
+/* ---- library ---------------------------------------------------------------------------------------------- */
+int         igg_version(void);
+const char* igg_last_error(void);
+
+/* ---- context life cycle ------------------------------------------------------------------------------------
+ * igg_create   replaces: allocate_bufs / allocate_custreams / init_cubufs_arrays (ref: src/update_halo.jl:126-148,
+ *              src/CUDAExt/update_halo.jl:60-76,155-159) -- but allocates lazily and grow-only inside the context.
+ * igg_destroy  replaces: free_update_halo_buffers / free_update_halo_cubuffers (ref: src/update_halo.jl:109-114,
+ *              src/CUDAExt/update_halo.jl:27-33), called from finalize_global_grid (ref: src/finalize_global_grid.jl:17).
+ */
+int igg_create(const igg_grid_desc* desc, igg_ctx** out);
+int igg_destroy(igg_ctx* ctx);
+
+/* ---- rank bootstrap (only needed when nprocs > 1) -----------------------------------------------------------
+ * Replaces the MPI message transport of the halo path (ref: src/update_halo.jl:343-367 MPI.Isend / MPI.Irecv!)
+ * by CUDA-IPC peer mappings that are set up once.  The library is transport agnostic: every rank exports an
+ * opaque blob, the CALLER all-gathers the blobs in rank order (MPI.Allgather in Julia, torch.distributed in the
+ * Python harness) and hands the concatenation back.  igg_bootstrap_import is collective over all ranks. */
+size_t igg_bootstrap_size(void);
+int    igg_bootstrap_export(igg_ctx* ctx, void* blob);
+int    igg_bootstrap_import(igg_ctx* ctx, const void* all_blobs, int nprocs);
+
+/* ---- update_halo! -------------------------------------------------------------------------------------------
+ * Replaces `_update_halo!(fields...; dims)` (ref: src/update_halo.jl:44-89) including iwrite_sendbufs! /
+ * iread_recvbufs! / wait_iwrite / wait_iread (ref: src/CUDAExt/update_halo.jl:143-203), the kernels write_d2x! /
+ * read_x2d! (:210-227), write_d2h_async! / read_h2d_async! (:230-251), sendrecv_halo_local / gpumemcopy!
+ * (ref: src/update_halo.jl:369-386, src/CUDAExt/update_halo.jl:257-259) and check_fields (:418-480).
+ * `dims_order` lists the dimensions (1..3) to update, the reference's `dims=` keyword (default (3,1,2)); the result
+ * does not depend on the order.  Collective over all ranks, same field list (sizes) on every rank.
+ * `stream` is a cudaStream_t (NULL = default stream); the call is ordered after prior work on it. */
+int igg_update_halo(igg_ctx* ctx, int nfields, const igg_field* fields,
+                    const int* dims_order, int ndims_order, void* stream, int flags);
+
+/* Select the exchange implementation (enum igg_mode).  IGG_MODE_NCCL_3PHASE needs igg_nccl_init first. */
+int igg_set_mode(igg_ctx* ctx, int mode);
+/* NCCL comparison path: rank 0 obtains an id (igg_nccl_unique_id_size bytes), the caller broadcasts it, every rank
+ * calls igg_nccl_init (collective). */
+size_t igg_nccl_unique_id_size(void);
+int    igg_nccl_get_unique_id(void* id_out);
+int    igg_nccl_init(igg_ctx* ctx, const void* id);
+
+/* ---- gather! ------------------------------------------------------------------------------------------------
+ * Replaces `gather!(A, A_global; root)` (ref: src/gather.jl:18-54, MPI.Gatherv! with a subarray datatype).
+ * Every rank passes its block `A` (sizeA, device or host memory); on `root`, `A_global` (sizeG, device or host
+ * memory) receives the block of the rank with coordinates (cx,cy,cz) at element offset (cx*sizeA[0], cy*sizeA[1],
+ * cz*sizeA[2]).  `A_global` may be NULL on non-root ranks.  Collective and host-synchronous like the reference. */
+int igg_gather(igg_ctx* ctx, const void* A, const int64_t sizeA[3], int ndimsA,
+               void* A_global, const int64_t sizeG[3], int ndimsG,
+               int elsize, int root, void* stream);
+
+/* ---- host-only helpers (no GPU needed) ----------------------------------------------------------------------
+ * igg_sendranges / igg_recvranges replace sendranges / recvranges (ref: src/update_halo.jl:281-302): n = 1|2,
+ * dim = 1..3, out = {x_lo,x_hi,y_lo,y_hi,z_lo,z_hi}, 1-based inclusive.  IGG_ERR_FIELDS if the field has no
+ * halo in `dim` ("Incoherent arguments: ol(A,dim)<2*halowidths[dim]."). */
+int igg_sendranges(const igg_grid_desc* desc, const igg_field* f, int n, int dim, int64_t out[6]);
+int igg_recvranges(const igg_grid_desc* desc, const igg_field* f, int n, int dim, int64_t out[6]);
+/* check_fields (ref: src/update_halo.jl:418-480): halowidth < 1, no halo at all, duplicates, differing types. */
+int igg_check_fields(const igg_grid_desc* desc, int nfields, const igg_field* fields);
+
+/* Plan inspection: the exact copy operations igg_update_halo would launch for this rank.  Used by the CPU tests
+ * to execute the plan of every simulated rank with numpy and compare against the oracle. */
+enum igg_op_kind { IGG_OP_PUSH = 0, IGG_OP_LOCAL = 1, IGG_OP_UNPACK = 2 };
+typedef struct igg_plan_op {
+    int32_t kind;           /* enum igg_op_kind */
+    int32_t field;          /* index into the field list */
+    int32_t offset[3];      /* neighbour offset o in {-1,0,1}^3 this op talks to */
+    int32_t peer;           /* rank at coords+o (== me for IGG_OP_LOCAL) */
+    int64_t src_lo[3], src_hi[3];  /* PUSH/LOCAL: source box in my field (1-based inclusive) */
+    int64_t dst_lo[3], dst_hi[3];  /* LOCAL/UNPACK: destination box in my field; PUSH: box in the peer's field */
+    int64_t staging_off;    /* PUSH: byte offset in the peer's staging half; UNPACK: in mine; LOCAL: -1 */
+    int64_t nbytes;         /* bytes moved by this op */
+    /* merged low-level form the kernel executes: `nz` planes of `ny` rows of `row_bytes` contiguous bytes */
+    int64_t src_off, dst_off, src_sy, src_sz, dst_sy, dst_sz;
+    int64_t row_bytes, ny, nz;
+    int32_t vec_bytes;      /* access width chosen from the alignment of all of the above */
+    int32_t ntiles;
+} igg_plan_op;
+int igg_plan_describe(const igg_grid_desc* desc, int nfields, const igg_field* fields,
+                      const int* dims_order, int ndims_order,
+                      igg_plan_op* ops_out, int ops_cap, int* nops_out, int64_t* staging_bytes_out);
+
+/* Control-plane self test (host only).  After the bootstrap the library talks between ranks through one POSIX
+ * shared-memory mailbox per rank (segment re-allocation hand-shakes, the barrier of gather!) -- the places where the
+ * reference would call MPI (ref: src/tools.jl:896-897 MPI.Barrier, src/gather.jl:49 MPI.Gatherv!).  These two calls
+ * run that mailbox across real processes without a GPU: create on every rank, exchange the 64-byte names, run. */
+int igg_ctrl_selftest_create(int me, int nprocs, char name_out[64], void** handle);
+int igg_ctrl_selftest_run(void* handle, int me, int nprocs, const char* names, int rounds);
+
+/* ---- introspection used by tests / bench ---------------------------------------------------------------------*/
+/* Number of kernels this context has launched so far (the bench's `gpu_launches`). */
+int64_t igg_launch_count(const igg_ctx* ctx);
+/* Name of the kernel symbol the update path launches (for profiles). */
+const char* igg_kernel_name(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* IGG_B200_H */
