@@ -19,9 +19,8 @@ DT = {1: np.uint8, 2: np.uint16, 4: np.uint32, 8: np.uint64, 16: np.complex128}
 
 def rand_field(shape, elsize, seed):
     if elsize == 16:
-        a = O.random_bits_field(tuple(shape) + (2,), 8, seed)
-        return np.asfortranarray(a.view(np.float64)[..., 0] + 1j * a.view(np.float64)[..., 1]) if False else \
-            np.asfortranarray(np.ascontiguousarray(a.reshape(-1, 2)).view(np.complex128).reshape(shape, order="F"))
+        n = int(np.prod(shape))
+        return O.random_bits_field((2 * n,), 8, seed).view(np.complex128).reshape(shape, order="F")
     return O.random_bits_field(shape, elsize, seed)
 
 
