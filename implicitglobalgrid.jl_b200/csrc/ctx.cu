@@ -244,12 +244,15 @@ static Plan* find_or_build_plan(igg_ctx* ctx, int nfields, const igg_field* fiel
 }
 
 static void order_after_previous(igg_ctx* ctx, cudaStream_t stream) {
-    // Calls on one context must execute in issue order (the staging double-buffer relies on it).
-    if (ctx->have_last && ctx->last_stream != stream) cudaStreamWaitEvent(stream, ctx->last_event, 0);
+    // Calls on one context must execute in issue order (the staging double-buffer relies on it).  Same stream: stream
+    // order does it for free.  Different stream: make the new stream wait for the tail of the previous one.
+    if (ctx->have_last && ctx->last_stream != stream) {
+        cudaEventRecord(ctx->last_event, ctx->last_stream);
+        cudaStreamWaitEvent(stream, ctx->last_event, 0);
+    }
 }
 
 static void remember_launch(igg_ctx* ctx, cudaStream_t stream) {
-    cudaEventRecord(ctx->last_event, stream);
     ctx->last_stream = stream;
     ctx->have_last = true;
     ctx->launches += 1;

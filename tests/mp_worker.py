@@ -1,0 +1,107 @@
+"""Multi-rank GPU parity worker: run under torchrun with one rank per GPU.
+
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 tests/mp_worker.py
+
+Every rank drives libigg_b200 through the public Python API (-> ctypes -> C ABI -> CUDA kernel with CUDA-IPC peer
+stores); rank 0 gathers all fields and compares them bitwise with the oracle simulating the same N ranks.
+Prints `MP_WORKER_OK <N>` on success.  (Test infrastructure: imports the oracle as the checker.)
+"""
+import os
+import sys
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+for p in (os.path.join(ROOT, "implicitglobalgrid.jl_b200"), ROOT):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+import igg_b200 as igg  # noqa: E402
+from oracle import igg_oracle as O  # noqa: E402
+
+TDT = {1: torch.uint8, 2: torch.int16, 4: torch.int32, 8: torch.int64}
+
+
+def case_list(n):
+    nx, ny, nz = 13, 9, 10
+    cases = [
+        # (grid size, kwargs, shapes, per-field hw or None, elsize, dims, repeats)
+        ((nx, ny, nz), dict(periodx=1, periody=1, periodz=1), [(nx, ny, nz)], None, 8, (3, 1, 2), 3),
+        ((nx, ny, nz), dict(), [(nx, ny, nz), (nx + 1, ny, nz), (nx, ny + 1, nz), (nx, ny, nz + 1)], None, 8, (3, 1, 2), 2),
+        ((nx, ny, nz), dict(periodx=1, periodz=1, overlaps=(4, 2, 3), halowidths=(2, 1, 1)),
+         [(nx, ny, nz), (nx + 1, ny, nz), (nx - 1, ny + 2, nz + 1)], None, 4, (3, 1, 2), 2),
+        ((nx, ny, nz), dict(periody=1, overlaps=(6, 4, 4), halowidths=(3, 1, 2)), [(nx, ny, nz), (nx, ny, nz + 1)], None, 2, (1, 3), 2),
+        ((nx, ny, nz), dict(periodx=1, periody=1, periodz=1, overlaps=(4, 4, 4), halowidths=(2, 2, 2)),
+         [(nx, ny, nz), (nx, ny, nz), (nx + 1, ny, nz)], [(2, 2, 2), (1, 1, 2), (2, 1, 1)], 8, (3, 1, 2), 2),
+        ((40, 30, 1), dict(periodx=1, periody=1), [(40, 30), (41, 30)], None, 8, (3, 1, 2), 2),
+        ((64, 1, 1), dict(periodx=1), [(64,), (65,)], None, 4, (3, 1, 2), 2),
+        # staging growth: a much bigger field after the small ones, then small again
+        ((96, 80, 72), dict(periodx=1, periody=1, periodz=1), [(96, 80, 72), (97, 80, 72)], None, 8, (3, 1, 2), 3),
+        ((nx, ny, nz), dict(periodx=1, periody=1, periodz=1), [(nx, ny, nz)], None, 1, (2, 1), 2),
+    ]
+    return cases
+
+
+def main():
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local_rank)
+    os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+    dist.init_process_group("gloo")
+    me, n = dist.get_rank(), dist.get_world_size()
+    ok = True
+    for ci, (gsz, kw, shapes, hws, elsize, dims, reps) in enumerate(case_list(n)):
+        try:
+            grids = O.make_grids(n, *gsz, **kw)
+        except O.IGGError:
+            continue
+        igg.init_global_grid(*gsz, quiet=True, **kw)
+        g = igg.global_grid()
+        assert g.dims == grids[me].dims and g.coords == grids[me].coords and g.neighbors == grids[me].neighbors
+        hws_ = hws or [g.halowidths] * len(shapes)
+        base = [O.random_bits_field(s, elsize, 1000 * ci + 10 * me + i) for i, s in enumerate(shapes)]
+        ts = [igg.from_numpy(a) for a in base]
+        for rep in range(reps):
+            igg.update_halo(*[(t, hw) for t, hw in zip(ts, hws_)], dims=dims, blocking=(rep % 2 == 0))
+        torch.cuda.synchronize()
+        mine = [igg.to_numpy(t).view(base[i].dtype) for i, t in enumerate(ts)]
+        out = [None] * n
+        dist.all_gather_object(out, mine)
+        if me == 0:
+            want = [[O.random_bits_field(s, elsize, 1000 * ci + 10 * r + i) for i, s in enumerate(shapes)] for r in range(n)]
+            O.update_halo(grids, [[(a, hw) for a, hw in zip(fr, hws_)] for fr in want], dims=dims)
+            for r in range(n):
+                for i in range(len(shapes)):
+                    if not np.array_equal(out[r][i], want[r][i]):
+                        ok = False
+                        bad = np.argwhere(out[r][i] != want[r][i])
+                        print(f"MISMATCH case {ci} rank {r} field {i}: {len(bad)} cells, first {bad[:4].tolist()}", flush=True)
+        # gather! of field 0 onto root 0 and onto the last rank (test/test_gather.jl:36-69,126-137)
+        for root in sorted({0, n - 1}):
+            A = ts[0]
+            dimsg = g.dims[:A.dim()]
+            if any(d > 1 for d in g.dims[A.dim():]):
+                continue
+            G = igg.zeros(tuple(s * d for s, d in zip(A.shape, dimsg)), dtype=A.dtype) if me == root else None
+            igg.gather(A, G, root=root)
+            blocks = [None] * n
+            dist.all_gather_object(blocks, igg.to_numpy(A))
+            if me == root:
+                wantG = np.zeros(tuple(G.shape), dtype=blocks[0].dtype, order="F")
+                O.gather(grids, blocks, wantG, root=root)
+                if not np.array_equal(igg.to_numpy(G), wantG):
+                    ok = False
+                    print(f"GATHER MISMATCH case {ci} root {root}", flush=True)
+        igg.finalize_global_grid()
+        dist.barrier()
+    flag = torch.tensor([1 if ok else 0])
+    dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+    if me == 0 and int(flag) == 1:
+        print(f"MP_WORKER_OK {n}", flush=True)
+    dist.destroy_process_group()
+    return 0 if int(flag) == 1 else 1
+
+
+if __name__ == "__main__":
+    sys.exit(main())
