@@ -77,6 +77,8 @@ def load():
         "igg_bootstrap_export": (C.c_int, [vp, vp]),
         "igg_bootstrap_import": (C.c_int, [vp, vp, i32]),
         "igg_update_halo": (C.c_int, [vp, i32, fp, i32p, i32, vp, i32]),
+        "igg_update_halo_noalloc": (C.c_int, [gd, i32, fp, i32p, i32, vp, i32]),
+        "igg_noalloc_scratch_bytes": (C.c_int64, []),
         "igg_set_mode": (C.c_int, [vp, i32]),
         "igg_nccl_unique_id_size": (C.c_size_t, []),
         "igg_nccl_get_unique_id": (C.c_int, [vp]),
@@ -101,7 +103,7 @@ def load():
 
 DECLARED_SYMBOLS = [
     "igg_version", "igg_last_error", "igg_create", "igg_destroy", "igg_bootstrap_size", "igg_bootstrap_export",
-    "igg_bootstrap_import", "igg_update_halo", "igg_set_mode", "igg_nccl_unique_id_size", "igg_nccl_get_unique_id",
+    "igg_bootstrap_import", "igg_update_halo", "igg_update_halo_noalloc", "igg_noalloc_scratch_bytes", "igg_set_mode", "igg_nccl_unique_id_size", "igg_nccl_get_unique_id",
     "igg_nccl_init", "igg_gather", "igg_sendranges", "igg_recvranges", "igg_check_fields", "igg_plan_describe",
     "igg_ctrl_selftest_create", "igg_ctrl_selftest_run", "igg_launch_count", "igg_kernel_name",
 ]

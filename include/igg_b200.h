@@ -120,6 +120,23 @@ int    igg_bootstrap_import(igg_ctx* ctx, const void* all_blobs, int nprocs);
 int igg_update_halo(igg_ctx* ctx, int nfields, const igg_field* fields,
                     const int* dims_order, int ndims_order, void* stream, int flags);
 
+/* igg_update_halo_noalloc -- no counterpart in the reference.
+ * The same halo update for callers that are not allowed to allocate device memory (a host application whose own pool
+ * owns the GPU, a library entered where an allocation would stall the caller's streams, a time loop that guarantees
+ * "no allocation after start-up").  It needs no context and never calls cudaMalloc / cudaFree / cudaHostAlloc: the
+ * kernel's scratch (its tile table and control words) is a fixed array inside the library image, reserved on every
+ * GPU that loads the library until the process exits (igg_noalloc_scratch_bytes() bytes, about 254 KiB).
+ * Restrictions: desc->nprocs must be 1 (periodic self-exchange only; ranks talking to each other need peer staging);
+ * a call may need at most IGG_NOALLOC_MAX_TILES tiles of 8 KiB halo data (about 25 MiB) -- larger calls return
+ * IGG_ERR_ARG with a message naming the limit.  All calls share the one array, which keeps the last call's contents:
+ * every call clears its control words and rewrites the table in stream order, so calls whose GPU work overlaps
+ * (different streams or host threads) race -- serialise them.  The first call on a device resolves the array's
+ * device address once; issue that first call before any stream capture begins.  `flags` as for igg_update_halo. */
+#define IGG_NOALLOC_MAX_TILES 3200
+int     igg_update_halo_noalloc(const igg_grid_desc* desc, int nfields, const igg_field* fields,
+                                const int* dims_order, int ndims_order, void* stream, int flags);
+int64_t igg_noalloc_scratch_bytes(void);
+
 /* Select the exchange implementation (enum igg_mode).  IGG_MODE_NCCL_3PHASE needs igg_nccl_init first. */
 int igg_set_mode(igg_ctx* ctx, int mode);
 /* NCCL comparison path: rank 0 obtains an id (igg_nccl_unique_id_size bytes), the caller broadcasts it, every rank
