@@ -23,8 +23,6 @@
 namespace igg {
 
 constexpr uint64_t kBlobMagic = 0x31424747495f4742ull;   // "BG_IGGB1"
-constexpr size_t kCtrlBytes = 8192;                      // 27 flags * 128 B + counters
-constexpr size_t kCountersOff = 4096;
 
 struct BootBlob {
     uint64_t magic;
@@ -36,6 +34,7 @@ struct BootBlob {
     char pad[96];
 };
 static_assert(sizeof(BootBlob) == 256, "BootBlob size");
+static_assert(sizeof(DeviceState) <= kFlagsOff, "DeviceState must fit before the flags");
 
 struct SegPayload {               // travels through the mailbox when a segment is (re)allocated
     uint64_t proc_nonce;
@@ -89,7 +88,6 @@ struct igg_ctx {
     std::vector<Peer> peers;
     bool bootstrapped = false;
     std::vector<std::unique_ptr<Plan>> plans;
-    unsigned long long epoch[IGG_NOFFSETS] = {0};
     int max_blocks = 0;
     int64_t launches = 0;
     cudaStream_t last_stream = nullptr;
@@ -103,14 +101,11 @@ struct igg_ctx {
     char* gather_src = nullptr;   int64_t gather_src_bytes = 0;   // staging for host-resident A
     TileRec* d_gather_tiles = nullptr; int gather_tiles_cap = 0;
     // NCCL comparison path (nccl_path.cu)
-    void* nccl = nullptr;
+    NcclPath* nccl = nullptr;
+    // optional kernel timeline (igg_trace_enable)
+    unsigned long long* d_trace = nullptr;
+    int last_grid = 0;
 };
-
-namespace igg {
-int nccl_update_halo(igg_ctx* ctx, int nfields, const igg_field* fields, int dims_mask, const int* order, int norder,
-                     cudaStream_t stream);
-void nccl_destroy(igg_ctx* ctx);
-}
 
 // ---- helpers -----------------------------------------------------------------------------------------------------
 
@@ -314,13 +309,15 @@ int igg_destroy(igg_ctx* ctx) {
     cudaSetDevice(ctx->device);
     cudaDeviceSynchronize();
     if (ctx->g.nprocs > 1 && ctx->cp.attached()) ctx->cp.barrier();   // nobody is still writing into my segments
-    nccl_destroy(ctx);
+    nccl_free(ctx->nccl);
+    ctx->nccl = nullptr;
     for (auto& p : ctx->peers) { close_segment(p.ctrl); close_segment(p.staging); close_segment(p.gather); }
     for (auto& pl : ctx->plans) if (pl->d_tiles) cudaFree(pl->d_tiles);
     if (ctx->staging) cudaFree(ctx->staging);
     if (ctx->gather_buf) cudaFree(ctx->gather_buf);
     if (ctx->gather_src) cudaFree(ctx->gather_src);
     if (ctx->d_gather_tiles) cudaFree(ctx->d_gather_tiles);
+    if (ctx->d_trace) cudaFree(ctx->d_trace);
     if (ctx->ctrl) cudaFree(ctx->ctrl);
     if (ctx->h_status) cudaFreeHost(ctx->h_status);
     if (ctx->last_event) cudaEventDestroy(ctx->last_event);
@@ -380,6 +377,52 @@ int igg_set_mode(igg_ctx* ctx, int mode) {
     return IGG_OK;
 }
 
+// The fused single-phase exchange for the dimensions in `dims_mask` (plan lookup, staging growth, one launch).
+static int launch_exchange(igg_ctx* ctx, int nfields, const igg_field* fields, int dims_mask, cudaStream_t stream) {
+    int rc;
+    Plan* plan = find_or_build_plan(ctx, nfields, fields, dims_mask, &rc);
+    if (!plan) return rc;
+    if (plan->tiles.empty()) return IGG_OK;                       // e.g. one rank, nothing periodic
+    if (plan->n_flags > (uint32_t)kMaxFlags)
+        return fail(IGG_ERR_ARG, "update_halo: this call needs %u arrival flags, the control segment holds %d; split the call.",
+                    plan->n_flags, kMaxFlags);
+    if (plan->active_mask && plan->staging_bytes > ctx->staging_half) {
+        rc = grow_staging(ctx, plan->staging_bytes);
+        if (rc) return rc;
+    }
+
+    KParams p;
+    std::memset(&p, 0, sizeof(p));
+    p.tiles = plan->d_tiles;
+    p.n_tiles = (int32_t)plan->tiles.size();
+    p.n_push_tiles = plan->n_push_tiles;
+    for (int i = 0; i < nfields; ++i) p.field[i] = fields[i].ptr;
+    p.local_flags = reinterpret_cast<const unsigned long long*>(ctx->ctrl + kFlagsOff);
+    p.state = reinterpret_cast<DeviceState*>(ctx->ctrl);       // epoch + staging parity live on the device
+    p.active_mask = plan->active_mask;
+    p.unpack_half = ctx->staging_half;
+    p.status = ctx->d_status;
+    p.timeout_ns = ctx->timeout_ns;
+    for (int oi = 0; oi < IGG_NOFFSETS; ++oi) {
+        if (!((plan->active_mask >> oi) & 1u)) continue;
+        const Peer& peer = ctx->peers[plan->peer[oi]];
+        p.push_base[oi] = peer.staging.ptr;
+        p.push_half[oi] = peer.staging.bytes;
+        p.unpack_base[oi] = ctx->staging;
+        p.remote_flags[oi] = reinterpret_cast<unsigned long long*>(peer.ctrl.ptr + kFlagsOff);
+    }
+    order_after_previous(ctx, stream);
+    if (ctx->d_trace) {
+        p.trace = ctx->d_trace;
+        ctx->last_grid = plan->grid;
+        CU(cudaMemsetAsync(ctx->d_trace, 0, (size_t)ctx->max_blocks * 8 * sizeof(unsigned long long), stream));
+    }
+    rc = launch_halo_kernel(p, plan->grid, stream);
+    if (rc) return rc;
+    remember_launch(ctx, stream);
+    return IGG_OK;
+}
+
 int igg_update_halo(igg_ctx* ctx, int nfields, const igg_field* fields_in, const int* dims_order, int ndims_order,
                     void* stream_v, int flags) {
     if (!ctx || !fields_in) return fail(IGG_ERR_ARG, "igg_update_halo: NULL argument.");
@@ -400,45 +443,30 @@ int igg_update_halo(igg_ctx* ctx, int nfields, const igg_field* fields_in, const
     }
 
     if (ctx->mode == IGG_MODE_NCCL_3PHASE && ctx->g.nprocs > 1) {
-        rc = nccl_update_halo(ctx, nfields, fields, dims_mask, dims_order, ndims_order, stream);
+        // Comparison path: the reference's dependent phases, in the caller's order (default z, x, y).
+        static const int kDefaultOrder[3] = {3, 1, 2};
+        const int* order = (dims_order && ndims_order > 0) ? dims_order : kDefaultOrder;
+        const int norder = (dims_order && ndims_order > 0) ? ndims_order : 3;
+        KParams proto;
+        std::memset(&proto, 0, sizeof(proto));
+        proto.local_flags = reinterpret_cast<const unsigned long long*>(ctx->ctrl + kFlagsOff);
+        proto.status = ctx->d_status;
+        proto.timeout_ns = ctx->timeout_ns;
+        order_after_previous(ctx, stream);
+        for (int q = 0; q < norder; ++q) {
+            const int d = order[q] - 1;
+            const int64_t l = ctx->g.neighbors[d][0], r = ctx->g.neighbors[d][1];
+            if (l < 0 && r < 0) continue;
+            if (l == ctx->g.me && r == ctx->g.me) rc = launch_exchange(ctx, nfields, fields, 1 << d, stream);   // local wrap
+            else rc = nccl_phase(ctx->nccl, ctx->g, nfields, fields, d, ctx->max_blocks, proto, stream, &ctx->launches);
+            if (rc) return rc;
+        }
+        ctx->last_stream = stream;
+        ctx->have_last = true;
+    } else {
+        rc = launch_exchange(ctx, nfields, fields, dims_mask, stream);
         if (rc) return rc;
-        if (!(flags & IGG_ASYNC)) CU(cudaStreamSynchronize(stream));
-        return IGG_OK;
     }
-
-    Plan* plan = find_or_build_plan(ctx, nfields, fields, dims_mask, &rc);
-    if (!plan) return rc;
-    if (plan->tiles.empty()) return IGG_OK;                       // e.g. one rank, nothing periodic
-    if (plan->active_mask && plan->staging_bytes > ctx->staging_half) {
-        rc = grow_staging(ctx, plan->staging_bytes);
-        if (rc) return rc;
-    }
-
-    KParams p;
-    std::memset(&p, 0, sizeof(p));
-    p.tiles = plan->d_tiles;
-    p.n_tiles = (int32_t)plan->tiles.size();
-    p.n_push_tiles = plan->n_push_tiles;
-    for (int i = 0; i < nfields; ++i) p.field[i] = fields[i].ptr;
-    p.local_flag = reinterpret_cast<const unsigned long long*>(ctx->ctrl);
-    p.push_count = reinterpret_cast<unsigned int*>(ctx->ctrl + kCountersOff);
-    p.status = ctx->d_status;
-    p.timeout_ns = ctx->timeout_ns;
-    for (int oi = 0; oi < IGG_NOFFSETS; ++oi) {
-        if (!((plan->active_mask >> oi) & 1u)) continue;
-        const Peer& peer = ctx->peers[plan->peer[oi]];
-        const unsigned long long ep = ++ctx->epoch[oi];
-        const int par = (int)(ep & 1ull);
-        p.epoch[oi] = ep;
-        p.expected[oi] = plan->expected[oi];
-        p.push_base[oi] = peer.staging.ptr + (int64_t)par * peer.staging.bytes;
-        p.unpack_base[oi] = ctx->staging + (int64_t)par * ctx->staging_half;
-        p.remote_flag[oi] = reinterpret_cast<unsigned long long*>(peer.ctrl.ptr) + (size_t)opposite_index(oi) * kFlagStrideU64;
-    }
-    order_after_previous(ctx, stream);
-    rc = launch_halo_kernel(p, plan->grid, stream);
-    if (rc) return rc;
-    remember_launch(ctx, stream);
     if (!(flags & IGG_ASYNC)) {
         CU(cudaStreamSynchronize(stream));
         return check_status(ctx);
@@ -573,8 +601,7 @@ int igg_gather(igg_ctx* ctx, const void* A, const int64_t sizeA_in[3], int ndims
     p.n_push_tiles = 0;
     p.field[0] = const_cast<char*>(src);
     p.push_base[0] = dst_base;
-    p.local_flag = reinterpret_cast<const unsigned long long*>(ctx->ctrl);
-    p.push_count = reinterpret_cast<unsigned int*>(ctx->ctrl + kCountersOff);
+    p.local_flags = reinterpret_cast<const unsigned long long*>(ctx->ctrl + kFlagsOff);
     p.status = ctx->d_status;
     p.timeout_ns = ctx->timeout_ns;
     order_after_previous(ctx, stream);
@@ -589,6 +616,40 @@ int igg_gather(igg_ctx* ctx, const void* A, const int64_t sizeA_in[3], int ndims
         CU(cudaStreamSynchronize(stream));
     }
     return ctx->cp.barrier();                // root's image may be overwritten by the next gather only after this
+}
+
+int igg_trace_enable(igg_ctx* ctx, int on) {
+    if (!ctx) return fail(IGG_ERR_ARG, "igg_trace_enable: NULL context.");
+    CU(cudaSetDevice(ctx->device));
+    CU(cudaDeviceSynchronize());
+    if (on && !ctx->d_trace) CU(cudaMalloc(&ctx->d_trace, (size_t)ctx->max_blocks * 8 * sizeof(unsigned long long)));
+    if (!on && ctx->d_trace) { CU(cudaFree(ctx->d_trace)); ctx->d_trace = nullptr; }
+    return IGG_OK;
+}
+
+int igg_trace_read(igg_ctx* ctx, uint64_t* out, int cap_blocks, int* nblocks_out) {
+    if (!ctx || !out || !nblocks_out) return fail(IGG_ERR_ARG, "igg_trace_read: NULL argument.");
+    if (!ctx->d_trace) return fail(IGG_ERR_STATE, "igg_trace_read: tracing is not enabled.");
+    CU(cudaSetDevice(ctx->device));
+    CU(cudaDeviceSynchronize());
+    const int n = ctx->last_grid < cap_blocks ? ctx->last_grid : cap_blocks;
+    CU(cudaMemcpy(out, ctx->d_trace, (size_t)n * 8 * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
+    *nblocks_out = n;
+    return IGG_OK;
+}
+
+size_t igg_nccl_unique_id_size(void) { return nccl_unique_id_size(); }
+
+int igg_nccl_get_unique_id(void* id_out) {
+    if (!id_out) return fail(IGG_ERR_ARG, "igg_nccl_get_unique_id: NULL argument.");
+    return nccl_get_unique_id(id_out);
+}
+
+int igg_nccl_init(igg_ctx* ctx, const void* id) {
+    if (!ctx || !id) return fail(IGG_ERR_ARG, "igg_nccl_init: NULL argument.");
+    if (ctx->nccl) return IGG_OK;
+    CU(cudaSetDevice(ctx->device));
+    return nccl_create(&ctx->nccl, ctx->g.nprocs, ctx->g.me, id);
 }
 
 int64_t igg_launch_count(const igg_ctx* ctx) { return ctx ? ctx->launches : 0; }

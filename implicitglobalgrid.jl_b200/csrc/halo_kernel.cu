@@ -2,22 +2,24 @@
 //
 // One launch per update_halo call does, for all fields and all 26 neighbour offsets:
 //   PUSH   pack a send box of my field and store it straight into the neighbour GPU's staging slot through its
-//          CUDA-IPC peer mapping (NVLink); when the last tile for a neighbour is done, publish an epoch in the
-//          neighbour's arrival flag (st.release.sys).
+//          CUDA-IPC peer mapping (NVLink); each 8-KiB tile is released on its own: barrier, fence.acq_rel.sys, then
+//          the call's epoch is stored into that tile's arrival flag on the neighbour.
 //   LOCAL  periodic wrap inside my own array (the rank is its own neighbour): send box -> opposite receive box.
-//   UNPACK wait for the neighbour's epoch (ld.acquire.sys), then copy its staged box into my receive box.
+//   UNPACK wait for the tile's arrival flag (ld.acquire.sys), then copy the staged tile into my receive box.
 // It replaces the reference's write_d2x! / read_x2d! kernels, the cuMemcpy3DAsync staging copies, the D2D
 // self-copy and the 12 host-blocking stream synchronisations per field
 // (ref: src/CUDAExt/update_halo.jl:153-259, src/update_halo.jl:51-88).
 //
 // Work is cut into tiles (TileRec, built on the host in plan.cpp); block b handles tiles b, b+grid, ...  Tiles are
-// ordered PUSH, LOCAL, UNPACK, so every block finishes (and signals) its pushes before it may spin on a flag.
+// ordered PUSH, LOCAL, UNPACK, so every block finishes (and flags) its pushes before it may spin on a flag.
 // The grid never exceeds the number of co-resident blocks, so spinning blocks cannot starve pushing ones.
 //
 // Pure data movement: bytes are copied as opaque 1/2/4/8/16-byte words, so results are bit-exact for any element
 // type.  No tensor cores, no shared-memory staging: each tile row is a contiguous run in both source and
 // destination, and strided x-faces degenerate to one element per row (inherent 32-byte-sector granularity).
 #include <cuda_runtime.h>
+
+#include <cstdlib>
 
 #include "igg_internal.h"
 
@@ -33,9 +35,11 @@ __device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long
     return v;
 }
 
-__device__ __forceinline__ void st_release_sys(unsigned long long* p, unsigned long long v) {
-    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+__device__ __forceinline__ void st_relaxed_sys(unsigned long long* p, unsigned long long v) {
+    asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
 }
+
+__device__ __forceinline__ void fence_acq_rel_sys() { asm volatile("fence.acq_rel.sys;" ::: "memory"); }
 
 __device__ __forceinline__ unsigned long long globaltimer_ns() {
     unsigned long long t;
@@ -45,13 +49,17 @@ __device__ __forceinline__ unsigned long long globaltimer_ns() {
 
 // Loads.  Field data was written by earlier kernels of this stream: default caching, no L1 allocation (streamed
 // once).  Staging data is written by a peer GPU during this kernel: read it at L2 (ld.cg), the point of coherence.
-template <typename V> __device__ __forceinline__ V load_stream(const V* p) { return __ldcs(p); }
+// LM selects the load flavour for field data: 0 = ld.global.cs, 1 = plain ld.global (used), 2 = ld.global.nc.
+// Measured on cfg2, cold L2: .cs 12.5 us per update, plain and .nc 9.6 us -- plain loads it is.
+template <typename V, int LM> __device__ __forceinline__ V load_stream(const V* p) {
+    if (LM == 0) return __ldcs(p);
+    if (LM == 2) return __ldg(p);
+    return *p;
+}
 template <typename V> __device__ __forceinline__ V load_l2(const V* p) { return __ldcg(p); }
-template <> __device__ __forceinline__ unsigned char load_stream(const unsigned char* p) { return *p; }
 template <> __device__ __forceinline__ unsigned char load_l2(const unsigned char* p) {
     return *reinterpret_cast<const volatile unsigned char*>(p);
 }
-template <> __device__ __forceinline__ unsigned short load_stream(const unsigned short* p) { return *p; }
 template <> __device__ __forceinline__ unsigned short load_l2(const unsigned short* p) {
     return *reinterpret_cast<const volatile unsigned short*>(p);
 }
@@ -92,10 +100,12 @@ __device__ __forceinline__ void item_offsets(const TileRec& t, uint32_t i, int64
 
 // Copies one tile; all loads of an unrolled group are issued before the first store (offsets are recomputed for
 // the stores instead of being kept live, which keeps the kernel within 64 registers = 4 blocks per SM).
-template <typename V, bool FROM_STAGING>
+template <typename V, bool FROM_STAGING, int LM>
 __device__ __forceinline__ void copy_tile(const TileRec& t, const char* __restrict__ src, char* __restrict__ dst) {
     constexpr int kUnroll = Unroll<V>::value;
     const uint32_t items = t.ncols * t.nrows;
+    // (An up-front prefetch.global.L2 of strided x-face rows was measured and did not help: those rows are bound by
+    // DRAM random-row throughput, 131 072 lines of 128 B per update at cfg2, not by the SM's miss queue.)
     for (uint32_t base = threadIdx.x; base < items; base += kThreads * kUnroll) {
         V v[kUnroll];
 #pragma unroll
@@ -105,7 +115,7 @@ __device__ __forceinline__ void copy_tile(const TileRec& t, const char* __restri
                 int64_t soff, doff;
                 item_offsets<V>(t, i, soff, doff);
                 const V* sp = reinterpret_cast<const V*>(src + soff);
-                v[u] = FROM_STAGING ? load_l2<V>(sp) : load_stream<V>(sp);
+                v[u] = FROM_STAGING ? load_l2<V>(sp) : load_stream<V, LM>(sp);
             }
         }
 #pragma unroll
@@ -120,52 +130,48 @@ __device__ __forceinline__ void copy_tile(const TileRec& t, const char* __restri
     }
 }
 
-template <bool FROM_STAGING>
+template <bool FROM_STAGING, int LM>
 __device__ __forceinline__ void copy_tile_dispatch(const TileRec& t, const char* src, char* dst) {
     switch (t.vec_log2) {
-        case 4: copy_tile<uint4, FROM_STAGING>(t, src, dst); break;
-        case 3: copy_tile<uint2, FROM_STAGING>(t, src, dst); break;
-        case 2: copy_tile<unsigned int, FROM_STAGING>(t, src, dst); break;
-        case 1: copy_tile<unsigned short, FROM_STAGING>(t, src, dst); break;
-        default: copy_tile<unsigned char, FROM_STAGING>(t, src, dst); break;
+        case 4: copy_tile<uint4, FROM_STAGING, LM>(t, src, dst); break;
+        case 3: copy_tile<uint2, FROM_STAGING, LM>(t, src, dst); break;
+        case 2: copy_tile<unsigned int, FROM_STAGING, LM>(t, src, dst); break;
+        case 1: copy_tile<unsigned short, FROM_STAGING, LM>(t, src, dst); break;
+        default: copy_tile<unsigned char, FROM_STAGING, LM>(t, src, dst); break;
     }
 }
 
-__global__ void __launch_bounds__(kThreads, 4) igg_halo_exchange_kernel(const __grid_constant__ KParams p) {
-    __shared__ unsigned int s_contrib[IGG_NOFFSETS];   // push tiles this block finished, per neighbour offset
-    if (threadIdx.x < IGG_NOFFSETS) s_contrib[threadIdx.x] = 0;
+template <int LM>
+__device__ __forceinline__ void halo_exchange_body(const KParams& p) {
+    __shared__ unsigned long long s_epoch;            // flag value of this launch (exchange launches so far + 1)
+    __shared__ unsigned int s_half[IGG_NOFFSETS];     // staging half (0/1) used with the neighbour at offset o
+    // Optional per-block timeline (igg_trace_enable): [0] globaltimer at start, then SM clock at [1] start,
+    // [2] first tile record loaded, [3] first copy issued, [4] first push flagged, [5] first flag seen, [6] end.
+#define IGG_TRACE(k) do { if (p.trace && threadIdx.x == 0) p.trace[(size_t)blockIdx.x * 8 + (k)] = (unsigned long long)clock64(); } while (0)
+    if (p.trace && threadIdx.x == 0) p.trace[(size_t)blockIdx.x * 8] = globaltimer_ns();
+    IGG_TRACE(1);
+
+    int ti = blockIdx.x;                              // grid <= n_tiles, so the first tile always exists
+    TileRec t = load_tile(p.tiles + ti);              // in flight together with the state loads below
+    if (p.state) {
+        if (threadIdx.x < IGG_NOFFSETS) s_half[threadIdx.x] = (__ldcg(&p.state->exchanges[threadIdx.x]) + 1u) & 1u;
+        if (threadIdx.x == 32) s_epoch = __ldcg(&p.state->call_epoch) + 1ull;
+    } else if (threadIdx.x < IGG_NOFFSETS) {
+        s_half[threadIdx.x] = 0;
+    }
     __syncthreads();
-    unsigned int arrived = 0;   // (thread 0 only) bit o: neighbour o's epoch has been observed by this block
+    if (p.trace && threadIdx.x == 0)   // [7]: what the block's first tile is (kind, vector width, rows, columns)
+        p.trace[(size_t)blockIdx.x * 8 + 7] = (unsigned long long)t.kind | ((unsigned long long)t.vec_log2 << 8) |
+                                              ((unsigned long long)t.nrows << 16) | ((unsigned long long)t.ncols << 40);
+    IGG_TRACE(2);
 
-    bool signalled = (int)blockIdx.x >= p.n_push_tiles;   // blocks without push tiles have nothing to signal
-
-    auto signal = [&]() {
-        // All data stores of this block -> visible system-wide before the counter / flag updates.
-        __syncthreads();
-        if (threadIdx.x < IGG_NOFFSETS) {
-            const unsigned int mine = s_contrib[threadIdx.x];
-            if (mine) {
-                __threadfence_system();
-                const unsigned int old = atomicAdd(p.push_count + threadIdx.x, mine);
-                if (old + mine == p.expected[threadIdx.x]) {      // last block for this neighbour
-                    p.push_count[threadIdx.x] = 0;                // ready for the next call (stream ordered)
-                    __threadfence_system();
-                    st_release_sys(p.remote_flag[threadIdx.x], p.epoch[threadIdx.x]);
-                }
-            }
-        }
-    };
-
-    for (int ti = blockIdx.x; ti < p.n_tiles; ti += gridDim.x) {
-        if (!signalled && ti >= p.n_push_tiles) { signal(); signalled = true; }
-
-        // Tile record: uniform across the block, five 16-byte read-only loads.
-        const TileRec t = load_tile(p.tiles + ti);
-
+    bool first = true;
+    while (true) {
         if (t.kind == IGG_OP_UNPACK) {
-            if (threadIdx.x == 0 && !((arrived >> t.nbr) & 1u)) {
-                const unsigned long long* flag = p.local_flag + (size_t)t.nbr * kFlagStrideU64;
-                const unsigned long long want = p.epoch[t.nbr];
+            // Wait until the neighbour has flagged this very tile (it flags each tile right after storing it).
+            if (threadIdx.x == 0) {
+                const unsigned long long* flag = p.local_flags + t.flag_idx;
+                const unsigned long long want = s_epoch;
                 unsigned long long t0 = 0;
                 unsigned int spins = 0;
                 while (ld_acquire_sys(flag) < want) {
@@ -175,20 +181,56 @@ __global__ void __launch_bounds__(kThreads, 4) igg_halo_exchange_kernel(const __
                         else if (now - t0 > p.timeout_ns) { *reinterpret_cast<volatile int*>(p.status) = IGG_ERR_TIMEOUT; break; }
                     }
                 }
-                arrived |= 1u << t.nbr;
+                if (first) IGG_TRACE(5);
             }
             __syncthreads();
-            copy_tile_dispatch<true>(t, p.unpack_base[t.nbr] + t.src_off, static_cast<char*>(p.field[t.field]) + t.dst_off);
+            const char* src = p.unpack_base[t.nbr] + (long long)s_half[t.nbr] * p.unpack_half + t.src_off;
+            copy_tile_dispatch<true, LM>(t, src, static_cast<char*>(p.field[t.field]) + t.dst_off);
+            if (first) IGG_TRACE(3);
         } else {
-            // PUSH: my field -> peer staging; LOCAL: my field -> my field; COPY (gather!): block -> peer array.
-            const char* src = static_cast<const char*>(p.field[t.field]) + t.src_off;
-            char* dst = (t.kind == IGG_OP_LOCAL ? static_cast<char*>(p.field[t.field]) : p.push_base[t.nbr]) + t.dst_off;
-            copy_tile_dispatch<false>(t, src, dst);
-            if (t.kind == IGG_OP_PUSH && threadIdx.x == 0) s_contrib[t.nbr] += 1;
+            // PUSH: my field -> peer staging; LOCAL: my field -> my field; COPY (gather!, NCCL pack): field -> buffer;
+            // COPY_IN (NCCL unpack): buffer filled by an earlier stream operation -> my field.
+            const char* src = (t.kind == kOpCopyIn ? p.unpack_base[t.nbr] : static_cast<const char*>(p.field[t.field])) + t.src_off;
+            char* dst;
+            if (t.kind == IGG_OP_LOCAL || t.kind == kOpCopyIn) dst = static_cast<char*>(p.field[t.field]) + t.dst_off;
+            else if (t.kind == IGG_OP_PUSH) dst = p.push_base[t.nbr] + (long long)s_half[t.nbr] * p.push_half[t.nbr] + t.dst_off;
+            else dst = p.push_base[t.nbr] + t.dst_off;
+            copy_tile_dispatch<false, LM>(t, src, dst);
+            if (first) IGG_TRACE(3);
+            if (t.kind == IGG_OP_PUSH) {
+                // Release this tile to the neighbour: all stores of the block (ordered before thread 0 by the barrier)
+                // become visible system-wide before the tile's arrival flag does.  Other warps move on to the next tile.
+                __syncthreads();
+                if (threadIdx.x == 0) {
+                    fence_acq_rel_sys();
+                    st_relaxed_sys(p.remote_flags[t.nbr] + t.flag_idx, s_epoch);
+                    if (first) IGG_TRACE(4);
+                }
+            }
+        }
+        first = false;
+        ti += gridDim.x;
+        if (ti >= p.n_tiles) break;
+        t = load_tile(p.tiles + ti);
+    }
+
+    // The last block to finish advances the exchange state for the next launch (stream-ordered after this one).
+    if (p.state && threadIdx.x == 0) {
+        __threadfence();
+        const unsigned int done = atomicAdd(&p.state->blocks_done, 1u);
+        if (done == gridDim.x - 1) {
+            p.state->blocks_done = 0;
+            p.state->call_epoch = s_epoch;
+            for (int o = 0; o < IGG_NOFFSETS; ++o)
+                if ((p.active_mask >> o) & 1u) p.state->exchanges[o] += 1u;
+            __threadfence();
         }
     }
-    if (!signalled) signal();
+    IGG_TRACE(6);
+#undef IGG_TRACE
 }
+
+__global__ void __launch_bounds__(kThreads, 4) igg_halo_exchange_kernel(const __grid_constant__ KParams p) { halo_exchange_body<1>(p); }
 
 }  // namespace
 

@@ -28,13 +28,23 @@ struct alignas(16) TileRec {
     uint8_t  kind;                              // igg_op_kind
     uint8_t  nbr;                               // neighbour offset index 0..26 (PUSH: target, UNPACK: source)
     uint8_t  pad[3];
-    uint32_t pad2[2];
+    uint32_t flag_idx;                          // PUSH: arrival flag to set at the receiver; UNPACK: flag to wait for
+    uint32_t pad2;
 };
 static_assert(sizeof(TileRec) == 80, "TileRec layout");
 
 constexpr int kThreads      = 256;      // threads per block of the halo kernel
 constexpr int kTileBytes    = 8192;     // bytes moved per tile
-constexpr int kFlagStrideU64 = 16;      // one arrival flag per 128-byte line
+constexpr size_t kFlagsOff   = 4096;    // control segment: arrival flags start here, one 8-byte word per tile
+constexpr int kMaxFlags      = 1 << 17; // 131 072 tiles per call (about 1 GiB of halo data)
+constexpr size_t kCtrlBytes  = kFlagsOff + (size_t)kMaxFlags * 8;
+
+// Per-context exchange state, first bytes of the control segment (private to the owning GPU).
+struct DeviceState {
+    unsigned long long call_epoch;             // exchange launches completed on this context
+    unsigned int exchanges[IGG_NOFFSETS];      // exchanges completed with the neighbour at offset o (staging parity)
+    unsigned int blocks_done;                  // blocks of the running launch that have finished
+};
 
 // Kernel parameters (passed by value, < 4 KB).
 struct KParams {
@@ -42,15 +52,21 @@ struct KParams {
     int32_t  n_tiles;
     int32_t  n_push_tiles;                     // tiles [0, n_push_tiles) are IGG_OP_PUSH
     void*    field[IGG_MAX_FIELDS];            // base pointers of the fields of this call
-    char*    push_base[IGG_NOFFSETS];          // peer staging half I write for the neighbour at offset o
-    const char* unpack_base[IGG_NOFFSETS];     // my staging half holding what the neighbour at offset o sent
-    unsigned long long* remote_flag[IGG_NOFFSETS];  // arrival flag in the peer's control segment (its slot -o)
-    const unsigned long long* local_flag;      // my arrival flags, [o * kFlagStrideU64]
-    unsigned int* push_count;                  // my per-offset counters of finished push tiles [27]
-    uint32_t expected[IGG_NOFFSETS];           // push tiles per offset in this plan
-    unsigned long long epoch[IGG_NOFFSETS];    // value to publish / wait for
+    char*    push_base[IGG_NOFFSETS];          // staging (half 0) of the peer at offset o; COPY tiles: plain destination
+    const char* unpack_base[IGG_NOFFSETS];     // my staging (half 0); COPY_IN tiles: plain source
+    long long push_half[IGG_NOFFSETS];         // bytes of one staging half on the peer at offset o
+    long long unpack_half;                     // bytes of one staging half of mine
+    unsigned long long* remote_flags[IGG_NOFFSETS];  // arrival-flag array in the control segment of the peer at offset o
+    const unsigned long long* local_flags;     // my arrival-flag array (written by my neighbours)
+    // Exchange state in my control segment (NULL for launches that exchange nothing: gather!, NCCL pack/unpack).
+    // It lives on the device so that the launch parameters do not change from call to call and an update_halo call
+    // can be captured into a CUDA graph and replayed: the kernel derives this call's epoch (flag value) and each
+    // neighbour's staging half from it and the last block to finish advances it.
+    DeviceState* state;
+    uint32_t active_mask;                      // bit o: this launch exchanges with the neighbour at offset o
     int*     status;                           // host-mapped status word (set on time-out)
     unsigned long long timeout_ns;
+    unsigned long long* trace;                 // optional per-block timeline (8 words per block), NULL = off
 };
 
 // ---- host-side plan ----------------------------------------------------------------------------------------
@@ -69,7 +85,7 @@ struct Plan {
     std::vector<igg_plan_op> ops;                    // PUSH ops, then LOCAL, then UNPACK
     std::vector<TileRec>     tiles;
     int32_t  n_push_tiles = 0;
-    uint32_t expected[IGG_NOFFSETS] = {0};
+    uint32_t n_flags = 0;                            // arrival flags this plan uses (must be <= kMaxFlags)
     uint32_t active_mask = 0;                        // bit o set: this plan exchanges with the neighbour at offset o
     int32_t  peer[IGG_NOFFSETS];                     // rank at offset o (or -1)
     int64_t  staging_bytes = 0;                      // bytes of one staging half this plan needs
@@ -95,10 +111,22 @@ int ranges(const igg_grid_desc& g, const igg_field& f, int n, int dim, bool send
 int build_plan(const igg_grid_desc& g, int nfields, const igg_field* fields, int dims_mask, Plan& plan);
 void build_block_copy_tiles(int64_t el, const int64_t ext[3], const int64_t dst_size[2], const int64_t dst_origin[3],
                             int64_t src_align, int64_t dst_align, std::vector<TileRec>& tiles);
-constexpr int kOpCopy = 3;   // internal tile kind: field[t.field] -> push_base[t.nbr], no signalling (gather!)
+constexpr int kOpCopy = 3;   // internal tile kind: field[t.field] -> push_base[t.nbr], no signalling (gather!, NCCL pack)
+constexpr int kOpCopyIn = 4; // internal tile kind: unpack_base[t.nbr] -> field[t.field], no waiting (NCCL unpack)
+int build_dim_phase(const igg_grid_desc& g, int nfields, const igg_field* fields, int d, std::vector<TileRec>& pack,
+                    std::vector<TileRec>& unpack, int64_t bytes[2]);
 // dims=(...) keyword -> bit mask of updated dimensions (NULL / empty = all three).
 int dims_mask_from_order(const int* dims_order, int n, int* mask_out);
 const char* last_error_cstr();
+
+// ---- NCCL comparison path (nccl_path.cu) ------------------------------------------------------------------
+struct NcclPath;
+size_t nccl_unique_id_size();
+int  nccl_get_unique_id(void* out);
+int  nccl_create(NcclPath** out, int nprocs, int me, const void* id_bytes);
+void nccl_free(NcclPath* np);
+int  nccl_phase(NcclPath* np, const igg_grid_desc& g, int nfields, const igg_field* fields, int d, int max_blocks,
+                const KParams& proto, void* stream, int64_t* launches);
 
 // ---- kernel launcher (halo_kernel.cu) ----------------------------------------------------------------------
 int  halo_kernel_max_coresident_blocks(int device);     // occupancy * SM count

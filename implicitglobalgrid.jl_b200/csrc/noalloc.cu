@@ -28,7 +28,7 @@
 namespace {
 
 constexpr int kMaxTiles = IGG_NOALLOC_MAX_TILES;
-constexpr size_t kControlBytes = 4096;   // arrival flags (unused with one rank), push counters, status word
+constexpr size_t kControlBytes = 4096;   // arrival flags (unused with one rank) and the status word
 constexpr size_t kScratchBytes = kControlBytes + (size_t)kMaxTiles * sizeof(igg::TileRec);
 constexpr int kMaxDevices = 64;
 
@@ -125,8 +125,7 @@ extern "C" int igg_update_halo_noalloc(const igg_grid_desc* desc, int nfields, c
     p.n_tiles = (int32_t)plan.tiles.size();
     p.n_push_tiles = 0;                                   // one rank: LOCAL tiles only
     for (int i = 0; i < nfields; ++i) p.field[i] = f[i].ptr;
-    p.local_flag = reinterpret_cast<const unsigned long long*>(scratch);
-    p.push_count = reinterpret_cast<unsigned int*>(scratch + 3584);
+    p.local_flags = reinterpret_cast<const unsigned long long*>(scratch);
     p.status = reinterpret_cast<int*>(scratch + 3968);
     p.timeout_ns = 1000000000ull;
     rc = launch_halo_kernel(p, (int)std::min<int64_t>((int64_t)plan.tiles.size(), max_blocks), stream);

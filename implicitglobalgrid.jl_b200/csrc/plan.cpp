@@ -264,7 +264,6 @@ int build_plan(const igg_grid_desc& g, int nfields, const igg_field* fields, int
     plan.dims_mask = dims_mask;
     plan.ops.clear();
     plan.tiles.clear();
-    std::fill(plan.expected, plan.expected + IGG_NOFFSETS, 0u);
     plan.active_mask = 0;
     plan.bytes_sent = 0;
 
@@ -281,6 +280,10 @@ int build_plan(const igg_grid_desc& g, int nfields, const igg_field* fields, int
     // Staging slots: one per (offset, field), identical on every rank (depends only on field sizes, halowidths and
     // the updated dimensions, never on which neighbours exist), so a sender can compute the receiver's layout.
     std::vector<int64_t> slot_off((size_t)IGG_NOFFSETS * nfields, -1);
+    // Arrival flags: one per tile.  A slot reserves an upper bound of the tiles any box that fits it can have
+    // (every full tile covers more than kTileBytes/2 bytes), so that flag numbers too are identical on every rank.
+    std::vector<uint32_t> slot_flag((size_t)IGG_NOFFSETS * nfields, 0);
+    uint32_t nflags = 0;
     int64_t total = 0;
     for (int oi = 0; oi < IGG_NOFFSETS; ++oi) {
         int o[3];
@@ -297,10 +300,13 @@ int build_plan(const igg_grid_desc& g, int nfields, const igg_field* fields, int
             if (!ok) continue;
             slot_off[(size_t)oi * nfields + i] = total;
             total += round_up(n, 128);
+            slot_flag[(size_t)oi * nfields + i] = nflags;
+            nflags += (uint32_t)(2 * ((n + kTileBytes - 1) / kTileBytes) + 1);
         }
     }
     plan.peer[13] = -1;
     plan.staging_bytes = total;
+    plan.n_flags = nflags;
 
     std::vector<igg_plan_op> push, local, unpack;
     std::vector<TileRec> tpush, tlocal, tunpack;
@@ -367,9 +373,11 @@ int build_plan(const igg_grid_desc& g, int nfields, const igg_field* fields, int
             } else {
                 op.kind = IGG_OP_PUSH;
                 op.staging_off = slot_off[(size_t)opposite_index(oi) * nfields + i];
+                const size_t first_push = tpush.size();
                 lower_op(f, i, IGG_OP_PUSH, oi, snd, snd, true, false, op.staging_off, op, tpush);
+                for (size_t k = first_push; k < tpush.size(); ++k)      // flag numbers in the RECEIVER's slot table
+                    tpush[k].flag_idx = slot_flag[(size_t)opposite_index(oi) * nfields + i] + (uint32_t)(k - first_push);
                 push.push_back(op);
-                plan.expected[oi] += (uint32_t)op.ntiles;
                 plan.active_mask |= 1u << oi;
                 plan.bytes_sent += op.nbytes;
 
@@ -384,7 +392,10 @@ int build_plan(const igg_grid_desc& g, int nfields, const igg_field* fields, int
                     up.src_lo[d] = up.src_hi[d] = 0;
                 }
                 up.staging_off = slot_off[(size_t)oi * nfields + i];
+                const size_t first_unpack = tunpack.size();
                 lower_op(f, i, IGG_OP_UNPACK, oi, rcv_mine, rcv_mine, false, true, up.staging_off, up, tunpack);
+                for (size_t k = first_unpack; k < tunpack.size(); ++k)
+                    tunpack[k].flag_idx = slot_flag[(size_t)oi * nfields + i] + (uint32_t)(k - first_unpack);
                 unpack.push_back(up);
             }
         }
@@ -407,6 +418,36 @@ void build_block_copy_tiles(int64_t el, const int64_t ext[3], const int64_t dst_
     const int64_t dsy = dst_size[0] * el, dsz = dst_size[0] * dst_size[1] * el;
     const int64_t dst_off = dst_origin[0] * el + dst_origin[1] * dsy + dst_origin[2] * dsz;
     emit_tiles(el, ext, 0, ext[0] * el, ext[0] * ext[1] * el, dst_off, dsy, dsz, src_align, dst_align, 0, 3 /*COPY*/, 0, tiles);
+}
+
+// One phase of the reference's scheme for dimension d (ref: src/update_halo.jl:51-88), used by the NCCL comparison
+// path: PACK tiles copy the send box of side n (full extent in the other dimensions) of every field that has a halo
+// in d into a contiguous per-side message (kind kOpCopy, base = push_base[n]); UNPACK tiles copy the per-side message
+// into the receive box of side n (kind kOpCopyIn, base = unpack_base[n]).  bytes[n] = message size of side n.
+int build_dim_phase(const igg_grid_desc& g, int nfields, const igg_field* fields, int d, std::vector<TileRec>& pack,
+                    std::vector<TileRec>& unpack, int64_t bytes[2]) {
+    bytes[0] = bytes[1] = 0;
+    for (int n = 0; n < 2; ++n) {
+        if (g.neighbors[d][n] < 0) continue;
+        int64_t off = 0;
+        for (int i = 0; i < nfields; ++i) {
+            const igg_field& f = fields[i];
+            if (field_ol(g, f, d) < 2 * f.halowidths[d]) continue;
+            int64_t r[6], ext[3];
+            const int64_t el = f.elsize, fsy = f.size[0] * el, fsz = f.size[0] * f.size[1] * el;
+            const int64_t align = (int64_t)((uintptr_t)f.ptr % 16);
+            ranges(g, f, n + 1, d + 1, true, r);
+            for (int k = 0; k < 3; ++k) ext[k] = r[2 * k + 1] - r[2 * k] + 1;
+            const int64_t foff_s = (r[0] - 1) * el + (r[2] - 1) * fsy + (r[4] - 1) * fsz;
+            emit_tiles(el, ext, foff_s, fsy, fsz, off, ext[0] * el, ext[0] * ext[1] * el, align, 0, i, kOpCopy, n, pack);
+            ranges(g, f, n + 1, d + 1, false, r);
+            const int64_t foff_r = (r[0] - 1) * el + (r[2] - 1) * fsy + (r[4] - 1) * fsz;
+            emit_tiles(el, ext, off, ext[0] * el, ext[0] * ext[1] * el, foff_r, fsy, fsz, 0, align, i, kOpCopyIn, n, unpack);
+            off += round_up(ext[0] * ext[1] * ext[2] * el, 128);
+        }
+        bytes[n] = off;
+    }
+    return IGG_OK;
 }
 
 }  // namespace igg

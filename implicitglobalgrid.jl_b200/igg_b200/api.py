@@ -325,6 +325,49 @@ def update_halo(*A, dims=(3, 1, 2), stream=None, blocking=True):
     return None
 
 
+def set_exchange_mode(mode):
+    """Selects how update_halo moves data between ranks: "ipc" (default: one fused kernel, peer stores over NVLink)
+    or "nccl" (comparison path: per-dimension pack kernel, grouped ncclSend/ncclRecv, unpack kernel).  Collective."""
+    g = global_grid()
+    lib = L.load()
+    if mode == "ipc":
+        L.check(lib.igg_set_mode(g.ctx, L.IGG_MODE_IPC_1PHASE))
+        return
+    if mode != "nccl":
+        raise ArgumentError(f"unknown exchange mode {mode!r} (use 'ipc' or 'nccl')")
+    if g.nprocs > 1:
+        n = lib.igg_nccl_unique_id_size()
+        buf = C.create_string_buffer(n)
+        if g.me == 0:
+            L.check(lib.igg_nccl_get_unique_id(buf))
+        ids = g.comm.allgather_bytes(buf.raw)
+        idb = C.create_string_buffer(ids[0], n)
+        L.check(lib.igg_nccl_init(g.ctx, idb))
+    L.check(lib.igg_set_mode(g.ctx, L.IGG_MODE_NCCL_3PHASE))
+
+
+def prepare_update_halo(*A, dims=(3, 1, 2), stream=None, blocking=True):
+    """Validates the arguments once and returns a zero-argument callable that performs `update_halo!(A...)` with
+    minimal host overhead (one foreign call).  For time loops that update the same arrays every step.  The arrays
+    must stay alive and in place; `stream` defaults to the stream current at preparation time."""
+    update_halo(*A, dims=dims, stream=stream, blocking=True)      # validates, builds the plan, warms the caches
+    key = (tuple(_field_key(a) for a in A), tuple(dims))
+    arr, nf, d, nd = _call_cache[key]
+    lib = L.load()
+    fn = lib.igg_update_halo
+    ctx = _grid.ctx
+    s = stream.cuda_stream if stream is not None else _torch().cuda.current_stream().cuda_stream
+    flags = L.IGG_SYNC if blocking else L.IGG_ASYNC
+    keep = (A, arr, d)                                            # keep the ctypes buffers and tensors alive
+
+    def call():
+        rc = fn(ctx, nf, arr, d, nd, s, flags)
+        if rc:
+            L.check(rc)
+        return keep and None
+    return call
+
+
 def gather(A, A_global, *, root=0, stream=None):
     """gather!(A, A_global; root=0)  -- ref: src/gather.jl:18-54.  `A_global` may be None on non-root ranks."""
     g = global_grid()

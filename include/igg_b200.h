@@ -193,6 +193,12 @@ int igg_ctrl_selftest_create(int me, int nprocs, char name_out[64], void** handl
 int igg_ctrl_selftest_run(void* handle, int me, int nprocs, const char* names, int rounds);
 
 /* ---- introspection used by tests / bench ---------------------------------------------------------------------*/
+/* Kernel timeline for profiling: when enabled, thread 0 of every block of the next update_halo launch records
+ * 8 words {globaltimer ns at start, SM clock at: start, first tile record loaded, first copy issued, pushes
+ * signalled, first arrival flag seen, end, unused}; igg_trace_read synchronises and copies the last launch's
+ * records (8 words per block, `*nblocks_out` blocks). */
+int igg_trace_enable(igg_ctx* ctx, int on);
+int igg_trace_read(igg_ctx* ctx, uint64_t* out, int cap_blocks, int* nblocks_out);
 /* Number of kernels this context has launched so far (the bench's `gpu_launches`). */
 int64_t igg_launch_count(const igg_ctx* ctx);
 /* Name of the kernel symbol the update path launches (for profiles). */

@@ -61,10 +61,43 @@ def main():
         assert g.dims == grids[me].dims and g.coords == grids[me].coords and g.neighbors == grids[me].neighbors
         hws_ = hws or [g.halowidths] * len(shapes)
         base = [O.random_bits_field(s, elsize, 1000 * ci + 10 * me + i) for i, s in enumerate(shapes)]
+        # the NCCL comparison path (reference-style dependent phases) must give the same bits as the fused kernel
+        if ci in (0, 1, 2, 4, 5):
+            igg.set_exchange_mode("nccl")
+            tn = [igg.from_numpy(a) for a in base]
+            for rep in range(2):
+                igg.update_halo(*[(t, hw) for t, hw in zip(tn, hws_)], dims=dims, blocking=(rep % 2 == 0))
+            torch.cuda.synchronize()
+            igg.set_exchange_mode("ipc")
+        else:
+            tn = None
         ts = [igg.from_numpy(a) for a in base]
         for rep in range(reps):
             igg.update_halo(*[(t, hw) for t, hw in zip(ts, hws_)], dims=dims, blocking=(rep % 2 == 0))
         torch.cuda.synchronize()
+        if ci in (0, 2):
+            # the same update captured into a CUDA graph and replayed twice (exchange state lives on the device)
+            tg = [igg.from_numpy(a) for a in base]
+            s = torch.cuda.Stream()
+            call = igg.prepare_update_halo(*[(t, hw) for t, hw in zip(tg, hws_)], dims=dims, stream=s, blocking=False)
+            torch.cuda.synchronize()
+            dist.barrier()
+            graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(graph, stream=s):
+                call()
+                call()
+            for rep in range(2):
+                graph.replay()
+            torch.cuda.synchronize()
+            for i, (a, b) in enumerate(zip(tg, ts)):
+                if not torch.equal(a, b):
+                    ok = False
+                    print(f"GRAPH/STREAM MISMATCH case {ci} rank {me} field {i}", flush=True)
+        if tn is not None:
+            for i, (a, b) in enumerate(zip(tn, ts)):
+                if not torch.equal(a, b):
+                    ok = False
+                    print(f"NCCL/IPC MISMATCH case {ci} rank {me} field {i}", flush=True)
         mine = [igg.to_numpy(t).view(base[i].dtype) for i, t in enumerate(ts)]
         out = [None] * n
         dist.all_gather_object(out, mine)
