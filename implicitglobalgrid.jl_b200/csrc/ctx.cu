@@ -169,6 +169,10 @@ static int grow_staging(igg_ctx* ctx, int64_t need_half) {
     int64_t half = std::max<int64_t>(need_half + need_half / 4, 1 << 20);
     half = (half + 0xfffff) & ~int64_t(0xfffff);
     CU(cudaMalloc(&ctx->staging, (size_t)(2 * half)));
+    // Touch the new memory and drain the device before any peer learns its handle: nothing of the allocation's
+    // set-up may still be pending when a neighbour's kernel starts storing into it.
+    CU(cudaMemset(ctx->staging, 0, (size_t)(2 * half)));
+    CU(cudaDeviceSynchronize());
     ctx->staging_half = half;
     std::vector<SegPayload> all;
     rc = exchange_segment(ctx, 0, half, 0, nullptr, all);
@@ -398,8 +402,7 @@ static int launch_exchange(igg_ctx* ctx, int nfields, const igg_field* fields, i
     p.n_push_tiles = plan->n_push_tiles;
     for (int i = 0; i < nfields; ++i) p.field[i] = fields[i].ptr;
     p.local_flags = reinterpret_cast<const unsigned long long*>(ctx->ctrl + kFlagsOff);
-    p.state = reinterpret_cast<DeviceState*>(ctx->ctrl);       // epoch + staging parity live on the device
-    p.active_mask = plan->active_mask;
+    p.state = reinterpret_cast<DeviceState*>(ctx->ctrl);       // epoch + staging parity live on the device    p.active_mask = plan->active_mask;
     p.unpack_half = ctx->staging_half;
     p.status = ctx->d_status;
     p.timeout_ns = ctx->timeout_ns;
@@ -616,6 +619,21 @@ int igg_gather(igg_ctx* ctx, const void* A, const int64_t sizeA_in[3], int ndims
         CU(cudaStreamSynchronize(stream));
     }
     return ctx->cp.barrier();                // root's image may be overwritten by the next gather only after this
+}
+
+int igg_debug_state(igg_ctx* ctx, uint64_t out[32]) {
+    if (!ctx || !out) return fail(IGG_ERR_ARG, "igg_debug_state: NULL argument.");
+    CU(cudaSetDevice(ctx->device));
+    CU(cudaDeviceSynchronize());
+    DeviceState st;
+    CU(cudaMemcpy(&st, ctx->ctrl, sizeof(st), cudaMemcpyDeviceToHost));
+    out[0] = st.call_epoch;
+    for (int o = 0; o < IGG_NOFFSETS; ++o) out[1 + o] = st.exchanges[o];
+    out[28] = st.blocks_done;
+    out[29] = (uint64_t)ctx->staging_half;
+    out[30] = (uint64_t)ctx->launches;
+    out[31] = 0;
+    return IGG_OK;
 }
 
 int igg_trace_enable(igg_ctx* ctx, int on) {

@@ -82,6 +82,7 @@ __device__ __forceinline__ TileRec load_tile(const TileRec* g) {
     t.vec_log2 = (uint8_t)((e.x >> 16) & 0xffu);
     t.kind = (uint8_t)(e.x >> 24);
     t.nbr = (uint8_t)(e.y & 0xffu);
+    t.flag_idx = e.z;
     return t;
 }
 

@@ -282,7 +282,7 @@ int build_plan(const igg_grid_desc& g, int nfields, const igg_field* fields, int
     std::vector<int64_t> slot_off((size_t)IGG_NOFFSETS * nfields, -1);
     // Arrival flags: one per tile.  A slot reserves an upper bound of the tiles any box that fits it can have
     // (every full tile covers more than kTileBytes/2 bytes), so that flag numbers too are identical on every rank.
-    std::vector<uint32_t> slot_flag((size_t)IGG_NOFFSETS * nfields, 0);
+    std::vector<uint32_t> slot_flag((size_t)IGG_NOFFSETS * nfields, 0), slot_nflag((size_t)IGG_NOFFSETS * nfields, 0);
     uint32_t nflags = 0;
     int64_t total = 0;
     for (int oi = 0; oi < IGG_NOFFSETS; ++oi) {
@@ -301,7 +301,8 @@ int build_plan(const igg_grid_desc& g, int nfields, const igg_field* fields, int
             slot_off[(size_t)oi * nfields + i] = total;
             total += round_up(n, 128);
             slot_flag[(size_t)oi * nfields + i] = nflags;
-            nflags += (uint32_t)(2 * ((n + kTileBytes - 1) / kTileBytes) + 1);
+            slot_nflag[(size_t)oi * nfields + i] = (uint32_t)(2 * ((n + kTileBytes - 1) / kTileBytes) + 1);
+            nflags += slot_nflag[(size_t)oi * nfields + i];
         }
     }
     plan.peer[13] = -1;
@@ -367,6 +368,7 @@ int build_plan(const igg_grid_desc& g, int nfields, const igg_field* fields, int
             if (peer == g.me) {
                 op.kind = IGG_OP_LOCAL;
                 op.staging_off = -1;
+                op.flag_base = -1;
                 lower_op(f, i, IGG_OP_LOCAL, oi, snd, rcv_peer, true, true, 0, op, tlocal);
                 local.push_back(op);
                 plan.bytes_sent += op.nbytes;
@@ -375,8 +377,11 @@ int build_plan(const igg_grid_desc& g, int nfields, const igg_field* fields, int
                 op.staging_off = slot_off[(size_t)opposite_index(oi) * nfields + i];
                 const size_t first_push = tpush.size();
                 lower_op(f, i, IGG_OP_PUSH, oi, snd, snd, true, false, op.staging_off, op, tpush);
+                if (tpush.size() - first_push > slot_nflag[(size_t)opposite_index(oi) * nfields + i])
+                    return fail(IGG_ERR_STATE, "internal: an exchange op has more tiles than its slot has arrival flags.");
                 for (size_t k = first_push; k < tpush.size(); ++k)      // flag numbers in the RECEIVER's slot table
                     tpush[k].flag_idx = slot_flag[(size_t)opposite_index(oi) * nfields + i] + (uint32_t)(k - first_push);
+                op.flag_base = (int32_t)slot_flag[(size_t)opposite_index(oi) * nfields + i];
                 push.push_back(op);
                 plan.active_mask |= 1u << oi;
                 plan.bytes_sent += op.nbytes;
@@ -396,6 +401,7 @@ int build_plan(const igg_grid_desc& g, int nfields, const igg_field* fields, int
                 lower_op(f, i, IGG_OP_UNPACK, oi, rcv_mine, rcv_mine, false, true, up.staging_off, up, tunpack);
                 for (size_t k = first_unpack; k < tunpack.size(); ++k)
                     tunpack[k].flag_idx = slot_flag[(size_t)oi * nfields + i] + (uint32_t)(k - first_unpack);
+                up.flag_base = (int32_t)slot_flag[(size_t)oi * nfields + i];
                 unpack.push_back(up);
             }
         }

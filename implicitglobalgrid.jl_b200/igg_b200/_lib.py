@@ -42,7 +42,7 @@ class PlanOp(C.Structure):
         ("staging_off", C.c_int64), ("nbytes", C.c_int64),
         ("src_off", C.c_int64), ("dst_off", C.c_int64), ("src_sy", C.c_int64), ("src_sz", C.c_int64),
         ("dst_sy", C.c_int64), ("dst_sz", C.c_int64), ("row_bytes", C.c_int64), ("ny", C.c_int64), ("nz", C.c_int64),
-        ("vec_bytes", C.c_int32), ("ntiles", C.c_int32),
+        ("vec_bytes", C.c_int32), ("ntiles", C.c_int32), ("flag_base", C.c_int32), ("reserved", C.c_int32),
     ]
 
 
@@ -90,6 +90,7 @@ def load():
         "igg_plan_describe": (C.c_int, [gd, i32, fp, i32p, i32, C.POINTER(PlanOp), i32, i32p, i64p]),
         "igg_ctrl_selftest_create": (C.c_int, [i32, i32, C.c_char_p, C.POINTER(vp)]),
         "igg_ctrl_selftest_run": (C.c_int, [vp, i32, i32, C.c_char_p, i32]),
+        "igg_debug_state": (C.c_int, [vp, C.POINTER(C.c_uint64)]),
         "igg_trace_enable": (C.c_int, [vp, i32]),
         "igg_trace_read": (C.c_int, [vp, C.POINTER(C.c_uint64), i32, i32p]),
         "igg_launch_count": (C.c_int64, [vp]),
@@ -107,7 +108,7 @@ DECLARED_SYMBOLS = [
     "igg_version", "igg_last_error", "igg_create", "igg_destroy", "igg_bootstrap_size", "igg_bootstrap_export",
     "igg_bootstrap_import", "igg_update_halo", "igg_update_halo_noalloc", "igg_noalloc_scratch_bytes", "igg_set_mode", "igg_nccl_unique_id_size", "igg_nccl_get_unique_id",
     "igg_nccl_init", "igg_gather", "igg_sendranges", "igg_recvranges", "igg_check_fields", "igg_plan_describe",
-    "igg_ctrl_selftest_create", "igg_ctrl_selftest_run", "igg_trace_enable", "igg_trace_read",
+    "igg_ctrl_selftest_create", "igg_ctrl_selftest_run", "igg_debug_state", "igg_trace_enable", "igg_trace_read",
     "igg_launch_count", "igg_kernel_name",
 ]
 

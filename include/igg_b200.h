@@ -180,6 +180,9 @@ typedef struct igg_plan_op {
     int64_t row_bytes, ny, nz;
     int32_t vec_bytes;      /* access width chosen from the alignment of all of the above */
     int32_t ntiles;
+    int32_t flag_base;      /* PUSH: first arrival flag set at the receiver (tile k sets flag_base + k); UNPACK: first
+                               flag waited for; LOCAL: -1 */
+    int32_t reserved;
 } igg_plan_op;
 int igg_plan_describe(const igg_grid_desc* desc, int nfields, const igg_field* fields,
                       const int* dims_order, int ndims_order,
@@ -197,6 +200,10 @@ int igg_ctrl_selftest_run(void* handle, int me, int nprocs, const char* names, i
  * 8 words {globaltimer ns at start, SM clock at: start, first tile record loaded, first copy issued, pushes
  * signalled, first arrival flag seen, end, unused}; igg_trace_read synchronises and copies the last launch's
  * records (8 words per block, `*nblocks_out` blocks). */
+/* Debug: the device-resident exchange state after synchronising the device: out[0] = exchange launches completed,
+ * out[1..27] = exchanges completed per neighbour offset, out[28] = blocks-done counter (0 between launches),
+ * out[29] = bytes of one staging half, out[30] = launches issued by the host. */
+int igg_debug_state(igg_ctx* ctx, uint64_t out[32]);
 int igg_trace_enable(igg_ctx* ctx, int on);
 int igg_trace_read(igg_ctx* ctx, uint64_t* out, int cap_blocks, int* nblocks_out);
 /* Number of kernels this context has launched so far (the bench's `gpu_launches`). */

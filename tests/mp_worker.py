@@ -61,22 +61,34 @@ def main():
         assert g.dims == grids[me].dims and g.coords == grids[me].coords and g.neighbors == grids[me].neighbors
         hws_ = hws or [g.halowidths] * len(shapes)
         base = [O.random_bits_field(s, elsize, 1000 * ci + 10 * me + i) for i, s in enumerate(shapes)]
+
+        def load(tensors, rep):
+            """Fresh data before every call: rep >= 0 -> throw-away data that differs from call to call (a stale read
+            of an earlier call's staging would show), rep < 0 -> the data the oracle is run on."""
+            torch.cuda.synchronize()
+            for i, t in enumerate(tensors):
+                a = base[i] if rep < 0 else O.random_bits_field(shapes[i], elsize, 777 + 1000 * ci + 100 * rep + 10 * me + i)
+                t.copy_(igg.from_numpy(a))
+            torch.cuda.synchronize()
+
         # the NCCL comparison path (reference-style dependent phases) must give the same bits as the fused kernel
         if ci in (0, 1, 2, 4, 5):
             igg.set_exchange_mode("nccl")
             tn = [igg.from_numpy(a) for a in base]
-            for rep in range(2):
-                igg.update_halo(*[(t, hw) for t, hw in zip(tn, hws_)], dims=dims, blocking=(rep % 2 == 0))
+            for rep in (0, -1):
+                load(tn, rep)
+                igg.update_halo(*[(t, hw) for t, hw in zip(tn, hws_)], dims=dims, blocking=(rep == 0))
             torch.cuda.synchronize()
             igg.set_exchange_mode("ipc")
         else:
             tn = None
         ts = [igg.from_numpy(a) for a in base]
-        for rep in range(reps):
+        for rep in list(range(reps)) + [-1]:
+            load(ts, rep)
             igg.update_halo(*[(t, hw) for t, hw in zip(ts, hws_)], dims=dims, blocking=(rep % 2 == 0))
         torch.cuda.synchronize()
         if ci in (0, 2):
-            # the same update captured into a CUDA graph and replayed twice (exchange state lives on the device)
+            # the same update captured into a CUDA graph and replayed (exchange state lives on the device)
             tg = [igg.from_numpy(a) for a in base]
             s = torch.cuda.Stream()
             call = igg.prepare_update_halo(*[(t, hw) for t, hw in zip(tg, hws_)], dims=dims, stream=s, blocking=False)
@@ -86,7 +98,8 @@ def main():
             with torch.cuda.graph(graph, stream=s):
                 call()
                 call()
-            for rep in range(2):
+            for rep in (0, 1, -1):
+                load(tg, rep)
                 graph.replay()
             torch.cuda.synchronize()
             for i, (a, b) in enumerate(zip(tg, ts)):

@@ -223,3 +223,35 @@ def test_c_ranges_match_reference_known_answers():
                         continue
                     assert rc == 0
                     assert [tuple(out[2 * k:2 * k + 2]) for k in range(3)] == want
+
+
+@pytest.mark.parametrize("topo,periods", [((2, 1, 1), (1, 1, 1)), ((2, 2, 1), (1, 1, 1)), ((2, 2, 2), (1, 1, 1)),
+                                          ((2, 2, 2), (0, 0, 0)), ((3, 2, 1), (1, 0, 1))])
+def test_arrival_flags_pair_up_and_never_collide(topo, periods):
+    """Every PUSH tile sets one arrival flag on the receiver and the matching UNPACK tile waits for exactly that
+    flag: sender and receiver must derive the same flag numbers and tile counts, and no two tiles arriving at one
+    rank may share a flag (a shared flag would let an unpack start before its data has landed)."""
+    nx, ny, nz = 40, 36, 33
+    grids = O.make_grids(int(np.prod(topo)), nx, ny, nz, dimx=topo[0], dimy=topo[1], dimz=topo[2],
+                         periodx=periods[0], periody=periods[1], periodz=periods[2])
+    hw = grids[0].halowidths
+    shapes = [(nx, ny, nz), (nx + 1, ny, nz)]
+    plans = []
+    for g in grids:
+        cf = [L.make_field(0x10000 * (i + 1), s, hw, 8) for i, s in enumerate(shapes)]
+        plans.append(L.plan_describe(desc_of(g), cf)[0])
+    for r, ops in enumerate(plans):
+        used = set()
+        for op in ops:
+            if op.kind != L.IGG_OP_UNPACK:
+                continue
+            rng = set(range(op.flag_base, op.flag_base + op.ntiles))
+            assert not (rng & used), "two arriving tiles share a flag"
+            used |= rng
+            # the sender's matching PUSH op: same field, opposite offset, aimed at me
+            o = tuple(op.offset)
+            match = [p for p in plans[op.peer] if p.kind == L.IGG_OP_PUSH and p.peer == r and p.field == op.field
+                     and tuple(p.offset) == tuple(-x for x in o)]
+            assert len(match) == 1
+            assert match[0].flag_base == op.flag_base and match[0].ntiles == op.ntiles
+            assert match[0].staging_off == op.staging_off and match[0].nbytes == op.nbytes
