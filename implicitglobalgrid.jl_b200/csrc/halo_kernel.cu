@@ -49,11 +49,13 @@ __device__ __forceinline__ unsigned long long globaltimer_ns() {
 
 // Loads.  Field data was written by earlier kernels of this stream: default caching, no L1 allocation (streamed
 // once).  Staging data is written by a peer GPU during this kernel: read it at L2 (ld.cg), the point of coherence.
-// LM selects the load flavour for field data: 0 = ld.global.cs, 1 = plain ld.global (used), 2 = ld.global.nc.
-// Measured on cfg2, cold L2: .cs 12.5 us per update, plain and .nc 9.6 us -- plain loads it is.
+// LM selects the load flavour for field data: 0 = ld.global.cs, 1 = plain ld.global (used), 2 = ld.global.nc,
+// 3 = ld.global.cg.  Measured on cfg2, cold L2: .cs 12.5 us per update, plain / .nc / .cg 9.6 us; every flavour makes
+// L2 fetch the whole 128-byte line of a strided x-face cell (595 k L2 read sectors for 222 k requested).
 template <typename V, int LM> __device__ __forceinline__ V load_stream(const V* p) {
     if (LM == 0) return __ldcs(p);
     if (LM == 2) return __ldg(p);
+    if (LM == 3) return __ldcg(p);
     return *p;
 }
 template <typename V> __device__ __forceinline__ V load_l2(const V* p) { return __ldcg(p); }
@@ -161,6 +163,17 @@ __device__ __forceinline__ void halo_exchange_body(const KParams& p) {
         s_half[threadIdx.x] = 0;
     }
     __syncthreads();
+    // Every block has now read the state it needs; the last block to get here advances it for the next launch
+    // (which is stream-ordered after this one).  Done early so that it is off the kernel's tail.
+    if (p.state && threadIdx.x == 0) {
+        const unsigned int seen = atomicAdd(&p.state->blocks_done, 1u);
+        if (seen == gridDim.x - 1) {
+            p.state->blocks_done = 0;
+            p.state->call_epoch = s_epoch;
+            for (int o = 0; o < IGG_NOFFSETS; ++o)
+                if ((p.active_mask >> o) & 1u) p.state->exchanges[o] += 1u;
+        }
+    }
     if (p.trace && threadIdx.x == 0)   // [7]: what the block's first tile is (kind, vector width, rows, columns)
         p.trace[(size_t)blockIdx.x * 8 + 7] = (unsigned long long)t.kind | ((unsigned long long)t.vec_log2 << 8) |
                                               ((unsigned long long)t.nrows << 16) | ((unsigned long long)t.ncols << 40);
@@ -215,24 +228,11 @@ __device__ __forceinline__ void halo_exchange_body(const KParams& p) {
         t = load_tile(p.tiles + ti);
     }
 
-    // The last block to finish advances the exchange state for the next launch (stream-ordered after this one).
-    if (p.state && threadIdx.x == 0) {
-        __threadfence();
-        const unsigned int done = atomicAdd(&p.state->blocks_done, 1u);
-        if (done == gridDim.x - 1) {
-            p.state->blocks_done = 0;
-            p.state->call_epoch = s_epoch;
-            for (int o = 0; o < IGG_NOFFSETS; ++o)
-                if ((p.active_mask >> o) & 1u) p.state->exchanges[o] += 1u;
-            __threadfence();
-        }
-    }
     IGG_TRACE(6);
 #undef IGG_TRACE
 }
 
 __global__ void __launch_bounds__(kThreads, 4) igg_halo_exchange_kernel(const __grid_constant__ KParams p) { halo_exchange_body<1>(p); }
-
 }  // namespace
 
 int halo_kernel_max_coresident_blocks(int device) {
