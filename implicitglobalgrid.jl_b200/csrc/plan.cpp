@@ -275,7 +275,8 @@ int build_plan(const igg_grid_desc& g, int nfields, const igg_field* fields, int
     std::vector<std::array<bool, 3>> halo(nfields);
     for (int i = 0; i < nfields; ++i)
         for (int d = 0; d < 3; ++d)
-            halo[i][d] = ((dims_mask >> d) & 1) && field_ol(g, fields[i], d) >= 2 * fields[i].halowidths[d];
+            halo[i][d] = ((dims_mask >> d) & 1) && field_ol(g, fields[i], d) >= 2 * fields[i].halowidths[d] &&
+                         (g.dims[d] > 1 || g.periods[d]);   // no rank has a neighbour in d otherwise (global fact)
 
     // Staging slots: one per (offset, field), identical on every rank (depends only on field sizes, halowidths and
     // the updated dimensions, never on which neighbours exist), so a sender can compute the receiver's layout.
@@ -291,13 +292,13 @@ int build_plan(const igg_grid_desc& g, int nfields, const igg_field* fields, int
         if (!o[0] && !o[1] && !o[2]) continue;
         plan.peer[oi] = -1;
         for (int i = 0; i < nfields; ++i) {
-            bool ok = true;
+            bool ok = true, remote = false;     // remote: the rank at this offset is another rank (on every rank alike)
             int64_t n = fields[i].elsize;
             for (int d = 0; d < 3; ++d) {
-                if (o[d]) { ok = ok && halo[i][d]; n *= fields[i].halowidths[d]; }
+                if (o[d]) { ok = ok && halo[i][d]; remote = remote || g.dims[d] > 1; n *= fields[i].halowidths[d]; }
                 else n *= fields[i].size[d];
             }
-            if (!ok) continue;
+            if (!ok || !remote) continue;       // self-wraps copy inside the array and need no staging slot
             slot_off[(size_t)oi * nfields + i] = total;
             total += round_up(n, 128);
             slot_flag[(size_t)oi * nfields + i] = nflags;
@@ -331,7 +332,12 @@ int build_plan(const igg_grid_desc& g, int nfields, const igg_field* fields, int
         plan.peer[oi] = (int32_t)peer;
 
         for (int i = 0; i < nfields; ++i) {
-            if (slot_off[(size_t)oi * nfields + i] < 0) continue;
+            bool has = true;
+            for (int d = 0; d < 3; ++d)
+                if (o[d]) has = has && halo[i][d];
+            if (!has) continue;
+            if (peer != g.me && slot_off[(size_t)oi * nfields + i] < 0)
+                return fail(IGG_ERR_STATE, "internal: exchange with another rank without a staging slot.");
             const igg_field& f = fields[i];
             Box snd, rcv_peer, rcv_mine;
             for (int d = 0; d < 3; ++d) {
