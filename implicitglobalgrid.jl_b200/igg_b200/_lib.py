@@ -84,6 +84,8 @@ def load():
         "igg_nccl_get_unique_id": (C.c_int, [vp]),
         "igg_nccl_init": (C.c_int, [vp, vp]),
         "igg_gather": (C.c_int, [vp, vp, i64p, i32, vp, i64p, i32, i32, i32, vp]),
+        "igg_diffusion3d_step": (C.c_int, [vp, vp, vp, i64p, C.c_double, C.c_double, C.c_double, C.c_double, C.c_double,
+                                           i32, vp]),
         "igg_sendranges": (C.c_int, [gd, fp, i32, i32, i64p]),
         "igg_recvranges": (C.c_int, [gd, fp, i32, i32, i64p]),
         "igg_check_fields": (C.c_int, [gd, i32, fp]),
@@ -107,7 +109,7 @@ def load():
 DECLARED_SYMBOLS = [
     "igg_version", "igg_last_error", "igg_create", "igg_destroy", "igg_bootstrap_size", "igg_bootstrap_export",
     "igg_bootstrap_import", "igg_update_halo", "igg_update_halo_noalloc", "igg_noalloc_scratch_bytes", "igg_set_mode", "igg_nccl_unique_id_size", "igg_nccl_get_unique_id",
-    "igg_nccl_init", "igg_gather", "igg_sendranges", "igg_recvranges", "igg_check_fields", "igg_plan_describe",
+    "igg_nccl_init", "igg_gather", "igg_diffusion3d_step", "igg_sendranges", "igg_recvranges", "igg_check_fields", "igg_plan_describe",
     "igg_ctrl_selftest_create", "igg_ctrl_selftest_run", "igg_debug_state", "igg_trace_enable", "igg_trace_read",
     "igg_launch_count", "igg_kernel_name",
 ]

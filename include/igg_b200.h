@@ -154,6 +154,18 @@ int igg_gather(igg_ctx* ctx, const void* A, const int64_t sizeA[3], int ndimsA,
                void* A_global, const int64_t sizeG[3], int ndimsG,
                int elsize, int root, void* stream);
 
+/* ---- the caller of the hot path: diffusion3D time step ------------------------------------------------------------
+ * One step of the reference's example (ref: examples/diffusion3D_multigpu_CuArrays_novis.jl:41-49, the five
+ * broadcasts qx, qy, qz, dTedt, T update) fused into one kernel: T2 = T + dt/Cp * div(lam grad T) on the inner cells,
+ * boundary cells copied, same operation order, IEEE double without FMA (bit-identical to the example's arithmetic).
+ * T, Cp, T2: dense column-major n[0] x n[1] x n[2] doubles on the current device.  part = 0 all cells, 1 = the two
+ * outermost layers (what update_halo! sends; do it first, then exchange while part 2 runs), 2 = the rest; adding 4 to
+ * `part` selects the bandwidth-bound arithmetic (divisions replaced by reciprocal multiplications, FMA allowed --
+ * agrees with the exact variant to ~1e-15 relative, not bit for bit).
+ * The caller then calls igg_update_halo on T2 and swaps T and T2. */
+int igg_diffusion3d_step(const double* T, const double* Cp, double* T2, const int64_t n[3], double lam, double dt,
+                         double dx, double dy, double dz, int part, void* stream);
+
 /* ---- host-only helpers (no GPU needed) ----------------------------------------------------------------------
  * igg_sendranges / igg_recvranges replace sendranges / recvranges (ref: src/update_halo.jl:281-302): n = 1|2,
  * dim = 1..3, out = {x_lo,x_hi,y_lo,y_hi,z_lo,z_hi}, 1-based inclusive.  IGG_ERR_FIELDS if the field has no

@@ -141,6 +141,21 @@ def main():
                     print(f"GATHER MISMATCH case {ci} root {root}", flush=True)
         igg.finalize_global_grid()
         dist.barrier()
+    # BASELINE config 1 on several ranks: the diffusion3D example, fused CUDA step + update_halo!, bit for bit
+    from igg_b200.diffusion3d import Diffusion3D
+    from oracle import diffusion_oracle as D
+    nd, nt = (40, 36, 33), 40
+    grids, Ts, Cps, dxyz, dt = D.setup(n, nd)
+    T0, Cp0 = Ts[me].copy(order="F"), Cps[me].copy(order="F")
+    want = D.run(grids, Ts, Cps, dxyz, dt, nt)[me] if True else None
+    for overlap in (False, True):
+        sim = Diffusion3D(*nd, T=T0, Cp=Cp0)
+        got = igg.to_numpy(sim.run(nt, overlap=overlap))
+        sim.finalize()
+        if not np.array_equal(got.view(np.uint64), want.view(np.uint64)):
+            ok = False
+            print(f"DIFFUSION MISMATCH rank {me} overlap {overlap}: max abs diff {np.abs(got - want).max()}", flush=True)
+        dist.barrier()
     flag = torch.tensor([1 if ok else 0])
     dist.all_reduce(flag, op=dist.ReduceOp.MIN)
     if me == 0 and int(flag) == 1:
