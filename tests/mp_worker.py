@@ -141,6 +141,43 @@ def main():
                     print(f"GATHER MISMATCH case {ci} root {root}", flush=True)
         igg.finalize_global_grid()
         dist.barrier()
+    # BASELINE config 2 at full size (256^3 f64, periodic): too big to ship to rank 0, so size-independent checks:
+    # (a) the fused path equals the NCCL path (itself checked against the oracle above) bit for bit, on the device;
+    # (b) after the update every halo plane equals the neighbour's send plane (checked through torch.distributed).
+    N = 256
+    igg.init_global_grid(N, N, N, periodx=1, periody=1, periodz=1, quiet=True)
+    g = igg.global_grid()
+    gen = torch.Generator(device="cuda")
+    gen.manual_seed(4321 + me)
+    a = igg.zeros((N, N, N), dtype=torch.int64)
+    a.copy_(torch.randint(-2**62, 2**62, (N, N, N), dtype=torch.int64, device="cuda", generator=gen))
+    b = a.clone(memory_format=torch.preserve_format)
+    igg.update_halo(a)
+    igg.set_exchange_mode("nccl")
+    igg.update_halo(b)
+    igg.set_exchange_mode("ipc")
+    torch.cuda.synchronize()
+    if not torch.equal(a, b):
+        ok = False
+        print(f"FULL-SIZE fused/NCCL MISMATCH rank {me}", flush=True)
+    for d in range(3):
+        right = g.neighbors[1][d]
+        left = g.neighbors[0][d]
+        mine_send = a.narrow(d, N - 2, 1).contiguous().cpu()        # my high-side send plane (ol=2, hw=1)
+        theirs = torch.empty_like(mine_send)
+        if right == me:
+            theirs = mine_send
+        else:
+            reqs = [dist.isend(mine_send, right, tag=10 + d), dist.irecv(theirs, left, tag=10 + d)]
+            for r_ in reqs:
+                r_.wait()
+        if not torch.equal(a.narrow(d, 0, 1).contiguous().cpu(), theirs):   # my low halo == left neighbour's high send
+            ok = False
+            print(f"FULL-SIZE halo/neighbour MISMATCH rank {me} dim {d}", flush=True)
+    del a, b
+    igg.finalize_global_grid()
+    dist.barrier()
+
     # BASELINE config 1 on several ranks: the diffusion3D example, fused CUDA step + update_halo!, bit for bit
     from igg_b200.diffusion3d import Diffusion3D
     from oracle import diffusion_oracle as D

@@ -257,6 +257,32 @@ def test_async_stream_ordered_call():
     assert bits_equal(t, want)
 
 
+@pytest.mark.parametrize("elsize", [12, 32, 36])
+def test_struct_elements_through_the_c_abi(elsize):
+    """Elements of any isbits size (CellArray B=1 cells of 2x2 Float64 = 32 B; 12- and 36-byte structs): torch has no
+    such dtype, so the field is a byte tensor handed to igg_update_halo directly."""
+    import ctypes as C
+    from igg_b200 import _lib as L
+    n = (17, 12, 9)
+    kw = dict(periodx=1, periody=1, periodz=1, overlaps=(4, 2, 2), halowidths=(2, 1, 1))
+    igg.init_global_grid(*n, quiet=True, **kw)
+    (g,) = O.make_grids(1, *n, **kw)
+    gg = igg.global_grid()
+    rng = np.random.default_rng(elsize)
+    dt = np.dtype((np.void, elsize))
+    shape = (n[0] + 1, n[1], n[2])
+    ncell = int(np.prod(shape))
+    a = np.frombuffer(rng.bytes(ncell * elsize), dtype=dt).reshape(shape, order="F").copy(order="F")
+    want = a.copy(order="F")
+    O.update_halo([g], [[(want, gg.halowidths)]], check=False)
+    raw = torch.from_numpy(a.reshape(-1, order="F").view(np.uint8).copy()).cuda()
+    f = L.make_field(raw.data_ptr(), shape, gg.halowidths, elsize)
+    arr = (L.Field * 1)(f)
+    L.check(L.load().igg_update_halo(gg.ctx, 1, arr, None, 0, C.c_void_p(torch.cuda.current_stream().cuda_stream), 0))
+    got = raw.cpu().numpy()
+    assert np.array_equal(got, want.reshape(-1, order="F").view(np.uint8))
+
+
 def test_cuda_graph_capture_and_replay():
     """The exchange state (epoch, staging parity) lives on the device, so a stream-ordered update_halo can be
     captured into a CUDA graph and replayed."""

@@ -255,3 +255,27 @@ def test_arrival_flags_pair_up_and_never_collide(topo, periods):
             assert len(match) == 1
             assert match[0].flag_base == op.flag_base and match[0].ntiles == op.ntiles
             assert match[0].staging_off == op.staging_off and match[0].nbytes == op.nbytes
+
+
+@pytest.mark.parametrize("elsize", [3, 12, 24, 32, 36])
+def test_struct_elements_cellarray_b1(elsize):
+    """Any isbits element size: a CellArray with B=1 is an array of cells of celllength*sizeof(T) bytes
+    (ref: src/shared.jl:288, 2x2 Float64 cells = 32 B in test/test_update_halo.jl:17-18); 12- and 36-byte structs too."""
+    grids = O.make_grids(4, 9, 7, 6, dimx=2, dimy=1, dimz=2, periodx=1, periody=1, periodz=1)
+    hw = grids[0].halowidths
+    shapes = [(9, 7, 6), (9, 8, 6)]
+    rng = np.random.default_rng(elsize)
+    dt = np.dtype((np.void, elsize))
+
+    def rnd(shape):
+        n = int(np.prod(shape))
+        return np.frombuffer(rng.bytes(n * elsize), dtype=dt).reshape(shape, order="F").copy(order="F")
+
+    base = [[rnd(s) for s in shapes] for _ in grids]
+    want = [[a.copy(order="F") for a in fr] for fr in base]
+    got = [[a.copy(order="F") for a in fr] for fr in base]
+    O.update_halo(grids, [[(a, hw) for a in fr] for fr in want], check=False)
+    execute_plans(grids, got, [hw, hw])
+    for r in range(len(grids)):
+        for i in range(len(shapes)):
+            assert np.array_equal(flat_bytes(got[r][i]), flat_bytes(want[r][i])), (r, i)
