@@ -187,6 +187,10 @@ __device__ __forceinline__ void halo_exchange_body(const KParams& p) {
     IGG_TRACE(2);
 
     bool first = true;
+    if (p.n_push_tiles < (int)gridDim.x) {            // rotation of the later waves, see the end of the loop
+        ti -= p.n_push_tiles;
+        if (ti < 0) ti += gridDim.x;
+    }
     while (true) {
         if (t.kind == IGG_OP_UNPACK) {
             // Wait until the neighbour has flagged this very tile (it flags each tile right after storing it).
@@ -229,6 +233,11 @@ __device__ __forceinline__ void halo_exchange_body(const KParams& p) {
                 }
             }
         }
+        // Later waves: tile w * grid + j goes to block (n_push_tiles + j) % grid, i.e. first to the blocks whose first
+        // tile was not a PUSH.  A block that has just pushed still has thread 0 inside the system-scope release fence
+        // (7-9 us at 8 GPUs); an UNPACK tile queued behind it would wait for that fence on top of its own flag.
+        // Every block still walks its tiles in increasing index, so all PUSH tiles (wave 0 whenever the rotation is
+        // non-zero) are issued before anything waits: the launch cannot deadlock.
         first = false;
         ti += gridDim.x;
         if (ti >= p.n_tiles) break;
@@ -239,7 +248,7 @@ __device__ __forceinline__ void halo_exchange_body(const KParams& p) {
 #undef IGG_TRACE
 }
 
-__global__ void __launch_bounds__(kThreads, 4) igg_halo_exchange_kernel(const __grid_constant__ KParams p) { halo_exchange_body<1>(p); }
+__global__ void __launch_bounds__(kThreads, kBlocksPerSM) igg_halo_exchange_kernel(const __grid_constant__ KParams p) { halo_exchange_body<1>(p); }
 }  // namespace
 
 int halo_kernel_max_coresident_blocks(int device) {

@@ -87,6 +87,18 @@ def main():
             load(ts, rep)
             igg.update_halo(*[(t, hw) for t, hw in zip(ts, hws_)], dims=dims, blocking=(rep % 2 == 0))
         torch.cuda.synchronize()
+        # The device-resident exchange state must have advanced once per call for every neighbour this rank
+        # exchanges with (it selects the staging half; stuck at 0 = no double buffering = a fast neighbour can
+        # overwrite staging that is still being unpacked).
+        import ctypes as C
+        from igg_b200 import _lib as L
+        st = (C.c_uint64 * 32)()
+        L.check(L.load().igg_debug_state(g.ctx, st))
+        counts = sorted(set(int(v) for v in st[1:28]))
+        if n > 1 and (int(st[0]) < reps + 1 or counts != [0, reps + 1]):
+            ok = False
+            print(f"EXCHANGE STATE case {ci} rank {me}: epoch {int(st[0])} per-neighbour counts {counts}, "
+                  f"want [0, {reps + 1}]", flush=True)
         if ci in (0, 2):
             # the same update captured into a CUDA graph and replayed (exchange state lives on the device)
             tg = [igg.from_numpy(a) for a in base]

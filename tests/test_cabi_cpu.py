@@ -59,6 +59,20 @@ def test_package_does_not_import_oracle():
                 assert "igg_oracle" not in txt and "import oracle" not in txt and "from oracle" not in txt, f
 
 
+def test_no_statement_hidden_in_a_trailing_comment():
+    """A lost newline once glued `p.active_mask = ...;` onto the end of a // comment, which silently disabled the
+    staging double buffering.  Flag any // comment that ends in what looks like a statement."""
+    pat = re.compile(r"//.*\S\s{3,}[A-Za-z_][\w.\->\[\]]*\s*(=|\+=|-=)\s*[^=].*;\s*$")
+    src = os.path.join(ROOT, "implicitglobalgrid.jl_b200", "csrc")
+    bad = []
+    for f in sorted(os.listdir(src)):
+        if f.endswith((".cu", ".cpp", ".h")):
+            for ln, line in enumerate(open(os.path.join(src, f), errors="replace"), 1):
+                if pat.search(line):
+                    bad.append(f"{f}:{ln}: {line.strip()[:100]}")
+    assert not bad, "\n".join(bad)
+
+
 def _ctrl_worker(me, nprocs, conn, rounds):
     sys.path.insert(0, os.path.join(ROOT, "implicitglobalgrid.jl_b200"))
     from igg_b200 import _lib as LL
