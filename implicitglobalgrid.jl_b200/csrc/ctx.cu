@@ -399,10 +399,7 @@ static int launch_exchange(igg_ctx* ctx, int nfields, const igg_field* fields, i
     std::memset(&p, 0, sizeof(p));
     p.tiles = plan->d_tiles;
     p.n_tiles = (int32_t)plan->tiles.size();
-    // The kernel uses n_push_tiles only to rotate the later tile waves away from the pushing blocks; IGG_NO_ROTATE=1
-    // turns that off (A/B measurements).
-    static const bool no_rotate = std::getenv("IGG_NO_ROTATE") && std::atoi(std::getenv("IGG_NO_ROTATE")) != 0;
-    p.n_push_tiles = no_rotate ? 0x7fffffff : plan->n_push_tiles;
+    p.n_push_tiles = plan->n_push_tiles;
     for (int i = 0; i < nfields; ++i) p.field[i] = fields[i].ptr;
     p.local_flags = reinterpret_cast<const unsigned long long*>(ctx->ctrl + kFlagsOff);
     p.state = reinterpret_cast<DeviceState*>(ctx->ctrl);       // epoch + staging parity live on the device
