@@ -87,6 +87,20 @@ def test_reference_full_update_fixtures(gargs, kw, shapes, widths, line, dtype):
     assert igg.x_g(2, 1.0, fields[0]) == O.x_g(g, 1, 2, 1.0, shapes[0][0])
 
 
+import golden_cases as G  # noqa: E402
+
+
+@pytest.mark.parametrize("ci,case", G.cases(1), ids=[c["name"] for _, c in G.cases(1)])
+def test_golden_single_rank(ci, case):
+    """The committed closed-form vectors (tests/golden/, built without the oracle): CUDA path == expected bits."""
+    igg.init_global_grid(*case["grid"], quiet=True, **G.kwargs(case))
+    hws = G.halowidths(case, igg.global_grid().halowidths)
+    fields = [igg.from_numpy(a) for a in G.arrays(ci, 0, "in")]
+    igg.update_halo(*[(t, hw) for t, hw in zip(fields, hws)], dims=tuple(case["dims"]))
+    for i, (t, want) in enumerate(zip(fields, G.arrays(ci, 0, "out"))):
+        assert bits_equal(t, want), (case["name"], i)
+
+
 @pytest.mark.parametrize("gargs,kw,shape,nohalo", [
     ((nx, ny, 1), dict(periodx=1, periody=1), (nx - 1, ny + 2), 0),                 # test/test_update_halo.jl:1135
     ((nx, ny, nz), dict(periodx=1, periody=1, periodz=1), (nx + 2, ny - 1, nz + 1), 1),  # :1150
