@@ -94,7 +94,7 @@ struct igg_ctx {
     cudaEvent_t last_event = nullptr;
     bool have_last = false;
     unsigned long long timeout_ns = 20ull * 1000000000ull;
-    struct PtrEntry { const void* user = nullptr; void* resolved = nullptr; };
+    struct PtrEntry { const void* user = nullptr; void* resolved = nullptr; bool host = false; };
     PtrEntry ptr_cache[64];
     // gather
     char* gather_buf = nullptr;   int64_t gather_bytes = 0;       // root: device image of A_global (peer mapped)
@@ -190,27 +190,28 @@ static int grow_staging(igg_ctx* ctx, int64_t need_half) {
 // through its device alias.  Pageable host memory is rejected (no CPU fallback, no hidden copies in update_halo).
 static int resolve_pointer(igg_ctx* ctx, const void* p, void** out, bool* is_host) {
     igg_ctx::PtrEntry& ce = ctx->ptr_cache[((uintptr_t)p >> 8) & 63];
-    if (!is_host && ce.user == p) { *out = ce.resolved; return IGG_OK; }
+    if (ce.user == p) { *out = ce.resolved; if (is_host) *is_host = ce.host; return IGG_OK; }
     cudaPointerAttributes a;
     cudaError_t e = cudaPointerGetAttributes(&a, p);
     if (e != cudaSuccess) { cudaGetLastError(); return fail(IGG_ERR_CUDA, "cudaPointerGetAttributes failed: %s", cudaGetErrorString(e)); }
     if (a.type == cudaMemoryTypeDevice || a.type == cudaMemoryTypeManaged) {
         *out = const_cast<void*>(p);
         if (is_host) *is_host = false;
-        ce.user = p; ce.resolved = *out;
+        ce.user = p; ce.resolved = *out; ce.host = false;
         return IGG_OK;
     }
     if (a.type == cudaMemoryTypeHost && a.devicePointer) {
         *out = a.devicePointer;
         if (is_host) *is_host = true;
-        ce.user = p; ce.resolved = *out;
+        ce.user = p; ce.resolved = *out; ce.host = true;
         return IGG_OK;
     }
     return fail(IGG_ERR_UNSUPPORTED,
                 "pointer %p is pageable host memory: pass device memory or page-locked (pinned/registered) host memory.", p);
 }
 
-static Plan* find_or_build_plan(igg_ctx* ctx, int nfields, const igg_field* fields, int dims_mask, int* rc_out) {
+static Plan* find_or_build_plan(igg_ctx* ctx, int nfields, const igg_field* fields, int dims_mask, const uint8_t* host_lines,
+                                int* rc_out) {
     for (auto& up : ctx->plans) {
         Plan* p = up.get();
         if (p->dims_mask != dims_mask || (int)p->key.size() != nfields) continue;
@@ -218,13 +219,14 @@ static Plan* find_or_build_plan(igg_ctx* ctx, int nfields, const igg_field* fiel
         for (int i = 0; i < nfields && same; ++i) {
             const FieldKey& k = p->key[i];
             const igg_field& f = fields[i];
-            same = k.elsize == f.elsize && k.ndims == f.ndims && k.align == (int32_t)((uintptr_t)f.ptr % 16);
+            same = k.elsize == f.elsize && k.ndims == f.ndims && k.align == (int32_t)((uintptr_t)f.ptr % 16) &&
+                   k.lines == ((host_lines && host_lines[i]) ? 1 : 0);
             for (int d = 0; d < 3 && same; ++d) same = k.size[d] == f.size[d] && k.hw[d] == f.halowidths[d];
         }
         if (same) { *rc_out = IGG_OK; return p; }
     }
     std::unique_ptr<Plan> plan(new Plan());
-    int rc = build_plan(ctx->g, nfields, fields, dims_mask, *plan);
+    int rc = build_plan(ctx->g, nfields, fields, dims_mask, *plan, host_lines);
     if (rc) { *rc_out = rc; return nullptr; }
     if (!plan->tiles.empty()) {
         cudaError_t e = cudaMalloc(&plan->d_tiles, plan->tiles.size() * sizeof(TileRec));
@@ -233,8 +235,18 @@ static Plan* find_or_build_plan(igg_ctx* ctx, int nfields, const igg_field* fiel
         if (e != cudaSuccess) { *rc_out = fail(IGG_ERR_CUDA, "plan upload failed: %s", cudaGetErrorString(e)); return nullptr; }
         plan->grid = (int)std::min<int64_t>((int64_t)plan->tiles.size(), ctx->max_blocks);
     }
+    if (!plan->wrap_tiles.empty()) {
+        cudaError_t e = cudaMalloc(&plan->d_wrap_tiles, plan->wrap_tiles.size() * sizeof(TileRec));
+        if (e == cudaSuccess)
+            e = cudaMemcpy(plan->d_wrap_tiles, plan->wrap_tiles.data(), plan->wrap_tiles.size() * sizeof(TileRec), cudaMemcpyHostToDevice);
+        if (e != cudaSuccess) { *rc_out = fail(IGG_ERR_CUDA, "plan upload failed: %s", cudaGetErrorString(e)); return nullptr; }
+    }
     if (ctx->plans.size() >= 64) {   // bound the cache (fields of ever-changing shapes)
-        if (ctx->plans.front()->d_tiles) { cudaDeviceSynchronize(); cudaFree(ctx->plans.front()->d_tiles); }
+        if (ctx->plans.front()->d_tiles || ctx->plans.front()->d_wrap_tiles) {
+            cudaDeviceSynchronize();
+            cudaFree(ctx->plans.front()->d_tiles);
+            cudaFree(ctx->plans.front()->d_wrap_tiles);
+        }
         ctx->plans.erase(ctx->plans.begin());
     }
     ctx->plans.push_back(std::move(plan));
@@ -316,7 +328,7 @@ int igg_destroy(igg_ctx* ctx) {
     nccl_free(ctx->nccl);
     ctx->nccl = nullptr;
     for (auto& p : ctx->peers) { close_segment(p.ctrl); close_segment(p.staging); close_segment(p.gather); }
-    for (auto& pl : ctx->plans) if (pl->d_tiles) cudaFree(pl->d_tiles);
+    for (auto& pl : ctx->plans) { cudaFree(pl->d_tiles); cudaFree(pl->d_wrap_tiles); }
     if (ctx->staging) cudaFree(ctx->staging);
     if (ctx->gather_buf) cudaFree(ctx->gather_buf);
     if (ctx->gather_src) cudaFree(ctx->gather_src);
@@ -382,10 +394,20 @@ int igg_set_mode(igg_ctx* ctx, int mode) {
 }
 
 // The fused single-phase exchange for the dimensions in `dims_mask` (plan lookup, staging growth, one launch).
-static int launch_exchange(igg_ctx* ctx, int nfields, const igg_field* fields, int dims_mask, cudaStream_t stream) {
+static int launch_exchange(igg_ctx* ctx, int nfields, const igg_field* fields, int dims_mask, cudaStream_t stream,
+                           const uint8_t* host_lines = nullptr) {
     int rc;
-    Plan* plan = find_or_build_plan(ctx, nfields, fields, dims_mask, &rc);
+    Plan* plan = find_or_build_plan(ctx, nfields, fields, dims_mask, host_lines, &rc);
     if (!plan) return rc;
+    if (!plan->wrap_tiles.empty()) {
+        // Whole-line x self-wrap of host-resident fields: its own kernel, independent of the other tiles of the call.
+        void* ptrs[IGG_MAX_FIELDS];
+        for (int i = 0; i < nfields; ++i) ptrs[i] = fields[i].ptr;
+        order_after_previous(ctx, stream);
+        rc = launch_wrap_lines_kernel(plan->d_wrap_tiles, (int)plan->wrap_tiles.size(), ptrs, nfields, stream);
+        if (rc) return rc;
+        remember_launch(ctx, stream);
+    }
     if (plan->tiles.empty()) return IGG_OK;                       // e.g. one rank, nothing periodic
     if (plan->n_flags > (uint32_t)kMaxFlags)
         return fail(IGG_ERR_ARG, "update_halo: this call needs %u arrival flags, the control segment holds %d; split the call.",
@@ -440,10 +462,15 @@ int igg_update_halo(igg_ctx* ctx, int nfields, const igg_field* fields_in, const
     CU(cudaSetDevice(ctx->device));
 
     igg_field fields[IGG_MAX_FIELDS];
+    uint8_t host_lines[IGG_MAX_FIELDS];
+    static const bool host_lines_enabled = !(std::getenv("IGG_HOST_LINES") && std::atoi(std::getenv("IGG_HOST_LINES")) == 0);
     for (int i = 0; i < nfields; ++i) {
         fields[i] = fields_in[i];
-        rc = resolve_pointer(ctx, fields_in[i].ptr, &fields[i].ptr, nullptr);
+        bool is_host = false;
+        rc = resolve_pointer(ctx, fields_in[i].ptr, &fields[i].ptr, &is_host);
         if (rc) return rc;
+        // Fields in page-locked host memory: whole-line x self-wrap (kOpWrapLines) unless IGG_HOST_LINES=0.
+        host_lines[i] = (is_host && host_lines_enabled && (uintptr_t)fields[i].ptr % 64 == 0) ? 1 : 0;
     }
 
     if (ctx->mode == IGG_MODE_NCCL_3PHASE && ctx->g.nprocs > 1) {
@@ -461,14 +488,14 @@ int igg_update_halo(igg_ctx* ctx, int nfields, const igg_field* fields_in, const
             const int d = order[q] - 1;
             const int64_t l = ctx->g.neighbors[d][0], r = ctx->g.neighbors[d][1];
             if (l < 0 && r < 0) continue;
-            if (l == ctx->g.me && r == ctx->g.me) rc = launch_exchange(ctx, nfields, fields, 1 << d, stream);   // local wrap
+            if (l == ctx->g.me && r == ctx->g.me) rc = launch_exchange(ctx, nfields, fields, 1 << d, stream, host_lines);   // local wrap
             else rc = nccl_phase(ctx->nccl, ctx->g, nfields, fields, d, ctx->max_blocks, proto, stream, &ctx->launches);
             if (rc) return rc;
         }
         ctx->last_stream = stream;
         ctx->have_last = true;
     } else {
-        rc = launch_exchange(ctx, nfields, fields, dims_mask, stream);
+        rc = launch_exchange(ctx, nfields, fields, dims_mask, stream, host_lines);
         if (rc) return rc;
     }
     if (!(flags & IGG_ASYNC)) {

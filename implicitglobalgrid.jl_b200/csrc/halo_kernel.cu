@@ -146,6 +146,48 @@ __device__ __forceinline__ void copy_tile_dispatch(const TileRec& t, const char*
     }
 }
 
+// kOpWrapLines (fields in page-locked host memory): periodic x self-wrap of `nrows` rows through whole 64-byte lines.
+// Eight neighbouring lanes own one row: lanes 0-3 its first line, lanes 4-7 its last line, so that every line is one
+// 64-byte request on the way in and on the way out (no partial write reaches the host's memory controller).
+// The halo cells are patched in shared memory: low halo <- high send, high halo <- low send.
+// A kernel of its own (one tile per block, launched on the same stream next to the exchange kernel): as a branch of
+// igg_halo_exchange_kernel it cost that kernel registers (spills at 4 blocks per SM).  It needs no ordering against
+// the other tiles of the call: they neither write these rows nor read the halo cells written here.
+struct WrapFields { void* field[IGG_MAX_FIELDS]; };
+
+__global__ void __launch_bounds__(kThreads) igg_wrap_lines_kernel(const TileRec* __restrict__ tiles, const __grid_constant__ WrapFields f) {
+    __shared__ uint4 s_lines[kThreads];               // one 16-byte piece of a host line per thread
+    const TileRec t = load_tile(tiles + blockIdx.x);
+    char* rows = static_cast<char*>(f.field[t.field]) + t.src_off;
+    const int64_t sy = t.src_sy, sz = t.src_sz, pitch = t.dst_off;
+    const int hwb = (int)t.dst_sy, olb = (int)t.dst_sz;
+    const uint32_t row0 = t.row0, ny = t.ny;
+    const uint32_t items = t.nrows * 8u;
+    for (uint32_t i0 = 0; i0 < items; i0 += kThreads) {
+        const uint32_t i = i0 + threadIdx.x;
+        const bool on = i < items;                      // whole groups of 8 lanes are on or off together
+        uint4* addr = nullptr;
+        if (on) {
+            const uint32_t row = row0 + (i >> 3), j = i & 7u;
+            uint32_t z = 0, y = row;
+            if (row >= ny) { z = row / ny; y = row - z * ny; }
+            addr = reinterpret_cast<uint4*>(rows + (int64_t)y * sy + (int64_t)z * sz + (j < 4 ? 0 : pitch - 128)) + j;
+            s_lines[threadIdx.x] = *addr;
+        }
+        __syncwarp();
+        if (on) {
+            unsigned char* L = reinterpret_cast<unsigned char*>(s_lines + (threadIdx.x & ~7u));   // [0,64) first line, [64,128) last
+            for (int b = (int)(i & 7u); b < hwb; b += 8) {
+                L[b] = L[128 - olb + b];                // low halo  <- high send
+                L[128 - hwb + b] = L[olb - hwb + b];    // high halo <- low send
+            }
+        }
+        __syncwarp();
+        if (on) *addr = s_lines[threadIdx.x];
+        __syncwarp();
+    }
+}
+
 template <int LM>
 __device__ __forceinline__ void halo_exchange_body(const KParams& p) {
     __shared__ unsigned long long s_epoch;            // flag value of this launch (exchange launches so far + 1)
@@ -273,6 +315,16 @@ int launch_halo_kernel(const KParams& p, int grid, void* stream) {
     cudaError_t e = cudaLaunchKernelEx(&cfg, igg_halo_exchange_kernel, p);
     if (e == cudaSuccess) e = cudaGetLastError();
     if (e != cudaSuccess) return fail(IGG_ERR_CUDA, "halo kernel launch failed: %s", cudaGetErrorString(e));
+    return IGG_OK;
+}
+
+int launch_wrap_lines_kernel(const TileRec* d_tiles, int n_tiles, void* const* fields, int nfields, void* stream) {
+    WrapFields f;
+    std::memset(&f, 0, sizeof(f));
+    for (int i = 0; i < nfields && i < IGG_MAX_FIELDS; ++i) f.field[i] = fields[i];
+    igg_wrap_lines_kernel<<<n_tiles, kThreads, 0, static_cast<cudaStream_t>(stream)>>>(d_tiles, f);
+    const cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return fail(IGG_ERR_CUDA, "wrap-lines kernel launch failed: %s", cudaGetErrorString(e));
     return IGG_OK;
 }
 

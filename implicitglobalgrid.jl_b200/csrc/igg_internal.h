@@ -78,6 +78,7 @@ struct FieldKey {
     int32_t elsize;
     int32_t ndims;
     int32_t align;       // ptr % 16
+    int32_t lines;       // 1: page-locked host field on a 64-byte boundary (x self-wrap may go through whole lines)
     bool operator==(const FieldKey& o) const { return std::memcmp(this, &o, sizeof(*this)) == 0; }
 };
 
@@ -95,6 +96,9 @@ struct Plan {
     // device copy (owned by the context)
     TileRec* d_tiles = nullptr;
     int      grid = 0;
+    // kOpWrapLines tiles of host-resident fields (run by igg_wrap_lines_kernel, one block each)
+    std::vector<TileRec>     wrap_tiles;
+    TileRec* d_wrap_tiles = nullptr;
 };
 
 inline int offset_index(const int o[3]) { return (o[0] + 1) + 3 * (o[1] + 1) + 9 * (o[2] + 1); }
@@ -109,12 +113,22 @@ inline int64_t field_ol(const igg_grid_desc& g, const igg_field& f, int d) {
 }
 int check_fields(const igg_grid_desc& g, int nfields, const igg_field* fields);
 int ranges(const igg_grid_desc& g, const igg_field& f, int n, int dim, bool send, int64_t out[6]);
-// Builds ops + tiles for this rank.  Pure host code.
-int build_plan(const igg_grid_desc& g, int nfields, const igg_field* fields, int dims_mask, Plan& plan);
+// Builds ops + tiles for this rank.  Pure host code.  `host_lines[i]` != 0 (optional): field i lives in page-locked
+// host memory on a 64-byte boundary, so its periodic x self-wrap may be emitted as kOpWrapLines tiles.
+int build_plan(const igg_grid_desc& g, int nfields, const igg_field* fields, int dims_mask, Plan& plan,
+               const uint8_t* host_lines = nullptr);
 void build_block_copy_tiles(int64_t el, const int64_t ext[3], const int64_t dst_size[2], const int64_t dst_origin[3],
                             int64_t src_align, int64_t dst_align, std::vector<TileRec>& tiles);
 constexpr int kOpCopy = 3;   // internal tile kind: field[t.field] -> push_base[t.nbr], no signalling (gather!, NCCL pack)
 constexpr int kOpCopyIn = 4; // internal tile kind: unpack_base[t.nbr] -> field[t.field], no waiting (NCCL unpack)
+// Internal tile kind for fields in page-locked HOST memory: the periodic x self-wrap of a row done through whole
+// 64-byte lines -- read the first and the last line of the row, copy low send -> high halo and high send -> low halo
+// in registers/shared memory, write both lines back whole.  Partial writes cost the host a read-modify-write per
+// cell (measured over PCIe: 65 536 strided 8-byte stores 328 us, the same rows as 64-byte lines 129 us).
+// TileRec use: src_off/src_sy/src_sz/row0/nrows/ny address the rows (x = 0); dst_off = row pitch in bytes,
+// dst_sy = halo width in bytes, dst_sz = overlap in bytes (<= 64); ncols = 8 lanes per row.
+constexpr int kOpWrapLines = 5;
+constexpr int kWrapRowsPerTile = 128;
 int build_dim_phase(const igg_grid_desc& g, int nfields, const igg_field* fields, int d, std::vector<TileRec>& pack,
                     std::vector<TileRec>& unpack, int64_t bytes[2]);
 // dims=(...) keyword -> bit mask of updated dimensions (NULL / empty = all three).
@@ -134,5 +148,7 @@ int  nccl_phase(NcclPath* np, const igg_grid_desc& g, int nfields, const igg_fie
 int  halo_kernel_max_coresident_blocks(int device);     // occupancy * SM count
 int  launch_halo_kernel(const KParams& p, int grid, void* stream);
 const char* halo_kernel_name();
+// kOpWrapLines tiles (host-resident fields), one block per tile, stream-ordered.
+int  launch_wrap_lines_kernel(const TileRec* d_tiles, int n_tiles, void* const* fields, int nfields, void* stream);
 
 }  // namespace igg

@@ -246,7 +246,8 @@ void lower_op(const igg_field& f, int field_idx, int kind, int nbr, const Box& s
 
 }  // namespace
 
-int build_plan(const igg_grid_desc& g, int nfields, const igg_field* fields, int dims_mask, Plan& plan) {
+int build_plan(const igg_grid_desc& g, int nfields, const igg_field* fields, int dims_mask, Plan& plan,
+               const uint8_t* host_lines) {
     int rc = check_grid(g);
     if (rc) return rc;
     rc = check_fields(g, nfields, fields);
@@ -259,11 +260,13 @@ int build_plan(const igg_grid_desc& g, int nfields, const igg_field* fields, int
         for (int d = 0; d < 3; ++d) { k.size[d] = fields[i].size[d]; k.hw[d] = fields[i].halowidths[d]; }
         k.elsize = fields[i].elsize; k.ndims = fields[i].ndims;
         k.align = (int32_t)((uintptr_t)fields[i].ptr % 16);
+        k.lines = (host_lines && host_lines[i]) ? 1 : 0;
         plan.key.push_back(k);
     }
     plan.dims_mask = dims_mask;
     plan.ops.clear();
     plan.tiles.clear();
+    plan.wrap_tiles.clear();
     plan.active_mask = 0;
     plan.bytes_sent = 0;
 
@@ -375,7 +378,35 @@ int build_plan(const igg_grid_desc& g, int nfields, const igg_field* fields, int
                 op.kind = IGG_OP_LOCAL;
                 op.staging_off = -1;
                 op.flag_base = -1;
-                lower_op(f, i, IGG_OP_LOCAL, oi, snd, rcv_peer, true, true, 0, op, tlocal);
+                // Host-resident field, pure x offset, the rank is its own x neighbour on both sides: the two
+                // x-face wraps of a row go through whole 64-byte lines (kOpWrapLines).  The op description stays
+                // the cell-level one; only the tiles differ.  Rows of this box are written by no other op, and the
+                // interior cells of the two lines are rewritten with the values just read.
+                const int64_t el = f.elsize, pitch = f.size[0] * el;
+                const bool lines = host_lines && host_lines[i] && o[0] && !o[1] && !o[2] && exists[0][0] && exists[0][1] &&
+                                   g.neighbors[0][0] == g.me && g.neighbors[0][1] == g.me && pitch % 64 == 0 &&
+                                   pitch >= 128 && field_ol(g, f, 0) * el <= 64;
+                if (lines) {
+                    std::vector<TileRec> unused;
+                    lower_op(f, i, IGG_OP_LOCAL, oi, snd, rcv_peer, true, true, 0, op, unused);
+                    if (o[0] < 0) {       // once per field: the -x op emits the tiles for both sides
+                        const int64_t ny = snd.hi[1] - snd.lo[1] + 1, nz = snd.hi[2] - snd.lo[2] + 1, rows = ny * nz;
+                        for (int64_t r0 = 0; r0 < rows; r0 += kWrapRowsPerTile) {
+                            TileRec t;
+                            std::memset(&t, 0, sizeof(t));
+                            t.src_off = (snd.lo[1] - 1) * pitch + (snd.lo[2] - 1) * pitch * f.size[1];
+                            t.src_sy = pitch; t.src_sz = pitch * f.size[1];
+                            t.dst_off = pitch; t.dst_sy = f.halowidths[0] * el; t.dst_sz = field_ol(g, f, 0) * el;
+                            t.row0 = (uint32_t)r0;
+                            t.nrows = (uint32_t)std::min<int64_t>(kWrapRowsPerTile, rows - r0);
+                            t.ncols = 8; t.ny = (uint32_t)ny;
+                            t.field = (uint16_t)i; t.vec_log2 = 4; t.kind = (uint8_t)kOpWrapLines; t.nbr = (uint8_t)oi;
+                            plan.wrap_tiles.push_back(t);
+                        }
+                    }
+                } else {
+                    lower_op(f, i, IGG_OP_LOCAL, oi, snd, rcv_peer, true, true, 0, op, tlocal);
+                }
                 local.push_back(op);
                 plan.bytes_sent += op.nbytes;
             } else {

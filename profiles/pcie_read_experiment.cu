@@ -51,6 +51,52 @@ __global__ void scatter8(char* __restrict__ host, const unsigned long long* __re
         *reinterpret_cast<unsigned long long*>(host + r * kPitch + x_off) = in[r];
 }
 
+// Write N16 x 16 bytes per row (16 = partial sector, 32 = one sector, 64 = a full host cache line).
+template <int N16>
+__global__ void scatter_wide(char* __restrict__ host, const unsigned long long* __restrict__ in) {
+    // N16 neighbouring lanes write the N16 x 16 bytes of one row in one store instruction (one request per row)
+    const long long total = (long long)gridDim.x * blockDim.x;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < kCells * N16; i += total) {
+        const long long r = i / N16;
+        const int k = (int)(i % N16);
+        const unsigned long long v = in[r];
+        uint4* p = reinterpret_cast<uint4*>(host + r * kPitch + 1024);      // mid-row: leaves the x-slabs alone
+        p[k] = make_uint4((unsigned)v, (unsigned)(v >> 32), k, 0);
+    }
+}
+
+// What a periodic single-rank update does with the x-slabs: host cell x=1 -> host cell x=255 and x=254 -> x=0.
+__global__ void wrap_x(char* __restrict__ host) {
+    const long long total = (long long)gridDim.x * blockDim.x;
+    for (long long r = (long long)blockIdx.x * blockDim.x + threadIdx.x; r < 2 * kCells; r += total) {
+        const long long row = r >> 1;
+        const long long so = (r & 1) ? 254 * 8 : 8, dofs = (r & 1) ? 0 : 255 * 8;
+        *reinterpret_cast<unsigned long long*>(host + row * kPitch + dofs) =
+            *reinterpret_cast<const unsigned long long*>(host + row * kPitch + so);
+    }
+}
+
+// The same through full 64-byte lines: read the first and the last line of a row, patch the halo cells, write both
+// lines back whole (no partial write reaches the host).
+__global__ void wrap_x_lines(char* __restrict__ host) {
+    // 8 neighbouring lanes per row: lanes 0-3 hold the first line (x = 0..7), lanes 4-7 the last one (x = 248..255);
+    // a warp instruction touches 4 rows x 2 lines, each line one 64-byte request.  65 536 rows * 8 lanes is a
+    // multiple of the grid stride for the grids used, so whole warps stay in the loop together.
+    const long long total = (long long)gridDim.x * blockDim.x;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < kCells * 8; i += total) {
+        const long long row = i >> 3;
+        const int j = (int)(i & 7);
+        uint4* p = reinterpret_cast<uint4*>(host + row * kPitch + (j < 4 ? 0 : kPitch - 128)) + j;
+        uint4 v = *p;
+        const int base = (threadIdx.x & 31) & ~7;
+        const unsigned s1x = __shfl_sync(0xffffffffu, v.z, base), s1y = __shfl_sync(0xffffffffu, v.w, base);          // x = 1
+        const unsigned s2x = __shfl_sync(0xffffffffu, v.x, base + 7), s2y = __shfl_sync(0xffffffffu, v.y, base + 7);  // x = 254
+        if (j == 0) { v.x = s2x; v.y = s2y; }           // x = 0   <- x = 254
+        if (j == 7) { v.z = s1x; v.w = s1y; }           // x = 255 <- x = 1
+        *p = v;
+    }
+}
+
 __global__ void contiguous(const uint4* __restrict__ host, uint4* __restrict__ out, long long n16) {
     const long long total = (long long)gridDim.x * blockDim.x;
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n16; i += total) out[i] = host[i];
@@ -97,6 +143,36 @@ int main() {
         printf("scatter 8 B x 65536 rows to host, %d blocks: %.1f us\n", g, timed([&] { scatter8<<<g, 256>>>(hd, out, 0); }));
     printf("read + write together (gather x=1, scatter x=0 on two streams would overlap; serial here): %.1f us\n",
            timed([&] { gather8<0><<<256, 256>>>(hd, out, 8); scatter8<<<256, 256>>>(hd, out, 0); }));
+    {   // gather and scatter at the same time on two streams: do PCIe reads hide behind PCIe writes?
+        cudaStream_t s1, s2;
+        unsigned long long* out2;
+        CK(cudaMalloc(&out2, bytes / kN));
+        CK(cudaMemset(out2, 1, bytes / kN));
+        CK(cudaStreamCreate(&s1));
+        CK(cudaStreamCreate(&s2));
+        cudaEvent_t a, b, c;
+        CK(cudaEventCreate(&a)); CK(cudaEventCreate(&b)); CK(cudaEventCreate(&c));
+        CK(cudaDeviceSynchronize());
+        CK(cudaEventRecord(a, s1));
+        CK(cudaStreamWaitEvent(s2, a, 0));
+        for (int i = 0; i < 10; ++i) { gather8<0><<<128, 256, 0, s1>>>(hd, out, 8); scatter8<<<128, 256, 0, s2>>>(hd, out2, 0); }
+        CK(cudaEventRecord(c, s2));
+        CK(cudaStreamWaitEvent(s1, c, 0));
+        CK(cudaEventRecord(b, s1));
+        CK(cudaEventSynchronize(b));
+        float ms;
+        CK(cudaEventElapsedTime(&ms, a, b));
+        printf("gather (stream 1) and scatter (stream 2) concurrently, one slab each: %.1f us per pair\n", ms * 100.f);
+    }
+    printf("scatter to host, one request per row of 16 B: %.1f us, 32 B: %.1f us, 64 B: %.1f us\n",
+           timed([&] { scatter_wide<1><<<256, 256>>>(hd, out); }), timed([&] { scatter_wide<2><<<256, 256>>>(hd, out); }),
+           timed([&] { scatter_wide<4><<<256, 256>>>(hd, out); }));
+    for (int g : {128, 512})
+        printf("periodic x-wrap inside host memory, both slabs (8-byte cells), %d blocks: %.1f us\n", g,
+               timed([&] { wrap_x<<<g, 256>>>(hd); }));
+    for (int g : {128, 512})
+        printf("the same through whole 64-byte lines (read 2 lines, write 2 lines per row), %d blocks: %.1f us\n", g,
+               timed([&] { wrap_x_lines<<<g, 256>>>(hd); }));
     uint4* big;
     CK(cudaMalloc(&big, 1 << 20));
     for (int g : {32, 148})

@@ -255,6 +255,51 @@ def test_pinned_host_fields_zero_copy():
         igg.update_halo(pageable)
 
 
+HOST_LINE_CASES = [
+    # (grid, kwargs, shapes, elsize, dims): page-locked host fields whose rows start on 64-byte boundaries take the
+    # whole-line x self-wrap (igg_wrap_lines_kernel); the others in the same call take the cell path.
+    ((32, 16, 12), dict(periodx=1, periody=1, periodz=1), [(32, 16, 12)], 8, (3, 1, 2)),
+    ((32, 16, 12), dict(periodx=1, periody=1, periodz=1), [(32, 16, 12), (33, 16, 12), (32, 17, 12)], 8, (3, 1, 2)),
+    ((32, 16, 12), dict(periodx=1), [(32, 16, 12)], 8, (3, 1, 2)),                      # x only periodic: all rows wrap
+    ((32, 16, 12), dict(periodx=1, periody=1, periodz=1, overlaps=(4, 2, 3), halowidths=(2, 1, 1)), [(32, 16, 12), (32, 16, 13)], 4, (3, 1, 2)),
+    ((16, 10, 9), dict(periodx=1, periody=1, periodz=1, overlaps=(6, 2, 2), halowidths=(3, 1, 1)), [(16, 10, 9)], 8, (3, 1, 2)),
+    ((8, 10, 9), dict(periodx=1, periody=1, periodz=1, overlaps=(4, 2, 2), halowidths=(2, 1, 1)), [(8, 10, 9)], 16, (1, 2)),
+    ((128, 9, 7), dict(periodx=1, periodz=1), [(128, 9, 7)], 1, (3, 1, 2)),
+    ((64, 40, 1), dict(periodx=1, periody=1), [(64, 40)], 2, (3, 1, 2)),
+    ((256, 1, 1), dict(periodx=1), [(256,)], 4, (3, 1, 2)),
+    ((32, 16, 300), dict(periodx=1, periody=1, periodz=1), [(32, 16, 300)], 8, (3, 1, 2)),   # many wrap tiles
+]
+
+
+@pytest.mark.parametrize("gsz,kw,shapes,elsize,dims", HOST_LINE_CASES, ids=[f"h{i}" for i in range(len(HOST_LINE_CASES))])
+def test_pinned_host_fields_whole_line_wrap(gsz, kw, shapes, elsize, dims):
+    igg.init_global_grid(*gsz, quiet=True, **kw)
+    (g,) = O.make_grids(1, *gsz, **kw)
+    tdt = {1: torch.uint8, 2: torch.int16, 4: torch.int32, 8: torch.int64, 16: torch.complex128}[elsize]
+    for rep in range(2):                                    # twice: the second call reuses the cached plan
+        base = [rand_any(s, elsize, 50 + 10 * rep + i) for i, s in enumerate(shapes)]
+        want = [a.copy(order="F") for a in base]
+        O.update_halo([g], [want], dims=dims)
+        ts = []
+        for a in base:
+            t = igg.zeros(a.shape, dtype=tdt, pin_memory=True)
+            t.copy_(igg.from_numpy(a, device="cpu"))
+            ts.append(t)
+        from igg_b200 import _lib as L
+        n0 = L.load().igg_launch_count(igg.global_grid().ctx)
+        igg.update_halo(*ts, dims=dims)
+        if kw.get("periody") and len(gsz) == 3 and gsz[1] > 1:
+            # exchange kernel + wrap-lines kernel: proves the whole-line path ran (the cell path is one launch)
+            assert L.load().igg_launch_count(igg.global_grid().ctx) - n0 == 2
+        for t, w in zip(ts, want):
+            assert bits_equal(t, w)
+    # the same bits as device-resident fields give
+    td = [igg.from_numpy(a) for a in base]
+    igg.update_halo(*td, dims=dims)
+    for t, w in zip(td, want):
+        assert bits_equal(t, w)
+
+
 def test_async_stream_ordered_call():
     igg.init_global_grid(32, 32, 32, periodx=1, periody=1, periodz=1, quiet=True)
     (g,) = O.make_grids(1, 32, 32, 32, periodx=1, periody=1, periodz=1)
