@@ -212,9 +212,10 @@ static int resolve_pointer(igg_ctx* ctx, const void* p, void** out, bool* is_hos
 
 static Plan* find_or_build_plan(igg_ctx* ctx, int nfields, const igg_field* fields, int dims_mask, const uint8_t* host_lines,
                                 int* rc_out) {
+    const bool ll128 = ctx->mode == IGG_MODE_IPC_LL128;
     for (auto& up : ctx->plans) {
         Plan* p = up.get();
-        if (p->dims_mask != dims_mask || (int)p->key.size() != nfields) continue;
+        if (p->dims_mask != dims_mask || (int)p->key.size() != nfields || p->ll128 != ll128) continue;
         bool same = true;
         for (int i = 0; i < nfields && same; ++i) {
             const FieldKey& k = p->key[i];
@@ -226,7 +227,7 @@ static Plan* find_or_build_plan(igg_ctx* ctx, int nfields, const igg_field* fiel
         if (same) { *rc_out = IGG_OK; return p; }
     }
     std::unique_ptr<Plan> plan(new Plan());
-    int rc = build_plan(ctx->g, nfields, fields, dims_mask, *plan, host_lines);
+    int rc = build_plan(ctx->g, nfields, fields, dims_mask, *plan, host_lines, ll128);
     if (rc) { *rc_out = rc; return nullptr; }
     if (!plan->tiles.empty()) {
         cudaError_t e = cudaMalloc(&plan->d_tiles, plan->tiles.size() * sizeof(TileRec));
@@ -308,6 +309,11 @@ int igg_create(const igg_grid_desc* desc, igg_ctx** out) {
     ctx->max_blocks = halo_kernel_max_coresident_blocks(ctx->device);
     if (ctx->max_blocks <= 0) return fail(IGG_ERR_CUDA, "occupancy query for the halo kernel failed (was the library built for sm_100a?): %s", cudaGetErrorString(cudaGetLastError()));
     if (const char* t = getenv("IGG_DEVICE_TIMEOUT_S")) ctx->timeout_ns = (unsigned long long)(atof(t) * 1e9);
+    // IGG_MODE=ll128 / fence: the IPC protocol a new context starts in (must be the same on every rank).
+    if (const char* m = getenv("IGG_MODE")) {
+        if (!strcmp(m, "ll128")) ctx->mode = IGG_MODE_IPC_LL128;
+        else if (!strcmp(m, "fence") || !strcmp(m, "ipc")) ctx->mode = IGG_MODE_IPC_1PHASE;
+    }
     ctx->peers.resize(desc->nprocs);
     if (desc->nprocs > 1) {
         rc = ctx->cp.create(desc->me, desc->nprocs, ctx->shm_name);
@@ -386,9 +392,23 @@ int igg_bootstrap_import(igg_ctx* ctx, const void* all_blobs, int nprocs) {
 
 int igg_set_mode(igg_ctx* ctx, int mode) {
     if (!ctx) return fail(IGG_ERR_ARG, "igg_set_mode: NULL context.");
-    if (mode != IGG_MODE_IPC_1PHASE && mode != IGG_MODE_NCCL_3PHASE) return fail(IGG_ERR_ARG, "igg_set_mode: unknown mode %d.", mode);
+    if (mode != IGG_MODE_IPC_1PHASE && mode != IGG_MODE_NCCL_3PHASE && mode != IGG_MODE_IPC_LL128)
+        return fail(IGG_ERR_ARG, "igg_set_mode: unknown mode %d.", mode);
     if (mode == IGG_MODE_NCCL_3PHASE && ctx->g.nprocs > 1 && !ctx->nccl)
         return fail(IGG_ERR_STATE, "igg_set_mode: call igg_nccl_init before selecting IGG_MODE_NCCL_3PHASE.");
+    const bool was_ll = ctx->mode == IGG_MODE_IPC_LL128, is_ll = mode == IGG_MODE_IPC_LL128;
+    if (was_ll != is_ll && ctx->g.nprocs > 1 && ctx->bootstrapped) {
+        // Entering or leaving the line format is collective: the other protocol's payload may sit where LL128 expects
+        // a line's epoch word, so the staging memory of every rank is cleared while nobody exchanges.
+        CU(cudaSetDevice(ctx->device));
+        CU(cudaDeviceSynchronize());
+        int rc = ctx->cp.barrier();
+        if (rc) return rc;
+        if (ctx->staging) CU(cudaMemset(ctx->staging, 0, (size_t)(2 * ctx->staging_half)));
+        CU(cudaDeviceSynchronize());
+        rc = ctx->cp.barrier();
+        if (rc) return rc;
+    }
     ctx->mode = mode;
     return IGG_OK;
 }
@@ -443,7 +463,7 @@ static int launch_exchange(igg_ctx* ctx, int nfields, const igg_field* fields, i
         ctx->last_grid = plan->grid;
         CU(cudaMemsetAsync(ctx->d_trace, 0, (size_t)ctx->max_blocks * 8 * sizeof(unsigned long long), stream));
     }
-    rc = launch_halo_kernel(p, plan->grid, stream);
+    rc = launch_halo_kernel(p, plan->grid, stream, plan->ll128);
     if (rc) return rc;
     remember_launch(ctx, stream);
     return IGG_OK;

@@ -188,7 +188,117 @@ __global__ void __launch_bounds__(kThreads) igg_wrap_lines_kernel(const TileRec*
     }
 }
 
-template <int LM>
+// ---- IGG_MODE_IPC_LL128: line-formatted staging (see igg_internal.h) -------------------------------------------
+__device__ __forceinline__ void st_volatile_v2(char* p, unsigned long long lo, unsigned long long hi) {
+    asm volatile("st.volatile.global.v2.u64 [%0], {%1, %2};" ::"l"(p), "l"(lo), "l"(hi) : "memory");
+}
+__device__ __forceinline__ void ld_volatile_v2(const char* p, unsigned long long& lo, unsigned long long& hi) {
+    asm volatile("ld.volatile.global.v2.u64 {%0, %1}, [%2];" : "=l"(lo), "=l"(hi) : "l"(p) : "memory");
+}
+
+// Position of payload byte `pb` of a box inside the field: merged rows of `rowb` bytes, ny rows per plane.
+struct BoxCursor {
+    int64_t off;          // byte offset from the box origin in the field
+    uint32_t c, y;        // byte within the row, row within the plane
+};
+__device__ __forceinline__ BoxCursor box_seek(int64_t pb, uint32_t rowb, uint32_t ny, int64_t sy, int64_t sz) {
+    const int64_t r = pb / rowb;
+    BoxCursor k;
+    k.c = (uint32_t)(pb - r * rowb);
+    const int64_t z = r / ny;
+    k.y = (uint32_t)(r - z * ny);
+    k.off = (int64_t)k.y * sy + z * sz + k.c;
+    return k;
+}
+template <int W>
+__device__ __forceinline__ void box_step(BoxCursor& k, uint32_t rowb, uint32_t ny, int64_t sy, int64_t sz) {
+    k.c += W; k.off += W;
+    if (k.c == rowb) {
+        k.c = 0; k.off += sy - (int64_t)rowb; k.y += 1;
+        if (k.y == ny) { k.y = 0; k.off += sz - (int64_t)ny * sy; }
+    }
+}
+template <int W> struct WordOf;
+template <> struct WordOf<1> { typedef unsigned char T; };
+template <> struct WordOf<2> { typedef unsigned short T; };
+template <> struct WordOf<4> { typedef unsigned int T; };
+template <> struct WordOf<8> { typedef unsigned long long T; };
+
+// PUSH: pack the lines [row0, row0 + nrows) of a slot and store them into the neighbour's staging, 8 lanes per line.
+template <int W>
+__device__ __forceinline__ void push_ll_tile(const TileRec& t, const char* __restrict__ box, char* __restrict__ slot,
+                                             unsigned long long epoch) {
+    typedef typename WordOf<W>::T Wt;
+    const uint32_t j = threadIdx.x & 7u;
+    for (uint32_t g = threadIdx.x >> 3; g < t.nrows; g += kThreads / 8) {
+        const int64_t line = (int64_t)t.row0 + g;
+        const int64_t pb = line * kLinePayload + 16 * j;
+        int nb = j == 7 ? 8 : 16;
+        if (pb + nb > t.dst_sy) nb = t.dst_sy > pb ? (int)(t.dst_sy - pb) : 0;
+        unsigned long long v[2] = {0ull, 0ull};
+        if (nb > 0) {
+            BoxCursor k = box_seek(pb, t.ncols, t.ny, t.src_sy, t.src_sz);
+#pragma unroll
+            for (int b = 0; b < 16; b += W) {
+                if (b < nb) {
+                    const unsigned long long w = *reinterpret_cast<const Wt*>(box + k.off);
+                    v[b >> 3] |= w << (8 * (b & 7));
+                    box_step<W>(k, t.ncols, t.ny, t.src_sy, t.src_sz);
+                }
+            }
+        }
+        if (j == 7) v[1] = epoch;
+        st_volatile_v2(slot + line * 128 + 16 * j, v[0], v[1]);
+    }
+}
+
+// UNPACK: wait for each line (its last 8 bytes equal this call's epoch), then scatter its payload into the field.
+// A warp polls its 4 lines together; returns false on time-out.
+template <int W>
+__device__ __forceinline__ bool unpack_ll_tile(const TileRec& t, char* __restrict__ box, const char* __restrict__ slot,
+                                               unsigned long long epoch, unsigned long long timeout_ns) {
+    typedef typename WordOf<W>::T Wt;
+    const uint32_t j = threadIdx.x & 7u, lane = threadIdx.x & 31u;
+    const uint32_t passes = (t.nrows + kThreads / 8 - 1) / (kThreads / 8);
+    for (uint32_t ps = 0; ps < passes; ++ps) {                 // every lane runs every pass (warp-wide votes below)
+        const uint32_t g = ps * (kThreads / 8) + (threadIdx.x >> 3);
+        const bool on = g < t.nrows;
+        const int64_t line = (int64_t)t.row0 + g;
+        const char* src = slot + line * 128 + 16 * j;
+        unsigned long long v[2] = {0ull, 0ull};
+        unsigned long long t0 = 0;
+        unsigned int spins = 0;
+        while (true) {
+            if (on) ld_volatile_v2(src, v[0], v[1]);
+            const unsigned long long flag = __shfl_sync(0xffffffffu, v[1], lane | 7u);
+            if (__all_sync(0xffffffffu, !on || flag == epoch)) break;
+            if ((++spins & 0x3ffu) == 0) {
+                unsigned long long now = globaltimer_ns();
+                now = __shfl_sync(0xffffffffu, now, 0);        // one clock for the whole warp: the exit must be uniform
+                if (t0 == 0) t0 = now;
+                else if (now - t0 > timeout_ns) return false;
+            }
+        }
+        if (on) {
+            const int64_t pb = line * kLinePayload + 16 * j;
+            int nb = j == 7 ? 8 : 16;
+            if (pb + nb > t.dst_sy) nb = t.dst_sy > pb ? (int)(t.dst_sy - pb) : 0;
+            if (nb > 0) {
+                BoxCursor k = box_seek(pb, t.ncols, t.ny, t.src_sy, t.src_sz);
+#pragma unroll
+                for (int b = 0; b < 16; b += W) {
+                    if (b < nb) {
+                        *reinterpret_cast<Wt*>(box + k.off) = (Wt)(v[b >> 3] >> (8 * (b & 7)));
+                        box_step<W>(k, t.ncols, t.ny, t.src_sy, t.src_sz);
+                    }
+                }
+            }
+        }
+    }
+    return true;
+}
+
+template <int LM, bool LL>
 __device__ __forceinline__ void halo_exchange_body(const KParams& p) {
     __shared__ unsigned long long s_epoch;            // flag value of this launch (exchange launches so far + 1)
     __shared__ unsigned int s_half[IGG_NOFFSETS];     // staging half (0/1) used with the neighbour at offset o
@@ -232,7 +342,29 @@ __device__ __forceinline__ void halo_exchange_body(const KParams& p) {
 
     bool first = true;
     while (true) {
-        if (t.kind == IGG_OP_UNPACK) {
+        if (LL && t.kind == kOpPushLL) {
+            const char* box = static_cast<const char*>(p.field[t.field]) + t.src_off;
+            char* slot = p.push_base[t.nbr] + (long long)s_half[t.nbr] * p.push_half[t.nbr] + t.dst_off;
+            switch (t.vec_log2) {
+                case 3: push_ll_tile<8>(t, box, slot, s_epoch); break;
+                case 2: push_ll_tile<4>(t, box, slot, s_epoch); break;
+                case 1: push_ll_tile<2>(t, box, slot, s_epoch); break;
+                default: push_ll_tile<1>(t, box, slot, s_epoch); break;
+            }
+            if (first) IGG_TRACE(3);
+        } else if (LL && t.kind == kOpUnpackLL) {
+            char* box = static_cast<char*>(p.field[t.field]) + t.src_off;
+            const char* slot = p.unpack_base[t.nbr] + (long long)s_half[t.nbr] * p.unpack_half + t.dst_off;
+            bool ok;
+            switch (t.vec_log2) {
+                case 3: ok = unpack_ll_tile<8>(t, box, slot, s_epoch, p.timeout_ns); break;
+                case 2: ok = unpack_ll_tile<4>(t, box, slot, s_epoch, p.timeout_ns); break;
+                case 1: ok = unpack_ll_tile<2>(t, box, slot, s_epoch, p.timeout_ns); break;
+                default: ok = unpack_ll_tile<1>(t, box, slot, s_epoch, p.timeout_ns); break;
+            }
+            if (!ok && (threadIdx.x & 31u) == 0) *reinterpret_cast<volatile int*>(p.status) = IGG_ERR_TIMEOUT;
+            if (first) IGG_TRACE(5);
+        } else if (!LL && t.kind == IGG_OP_UNPACK) {
             // Wait until the neighbour has flagged this very tile (it flags each tile right after storing it).
             if (threadIdx.x == 0) {
                 const unsigned long long* flag = p.local_flags + t.flag_idx;
@@ -262,7 +394,7 @@ __device__ __forceinline__ void halo_exchange_body(const KParams& p) {
             else dst = p.push_base[t.nbr] + t.dst_off;
             copy_tile_dispatch<false, LM>(t, src, dst);
             if (first) IGG_TRACE(3);
-            if (t.kind == IGG_OP_PUSH) {
+            if (!LL && t.kind == IGG_OP_PUSH) {
                 // Release this tile to the neighbour: all stores of the block (ordered before thread 0 by the barrier)
                 // become visible system-wide before the tile's arrival flag does.  Other warps move on to the next tile.
                 __syncthreads();
@@ -287,17 +419,20 @@ __device__ __forceinline__ void halo_exchange_body(const KParams& p) {
 #undef IGG_TRACE
 }
 
-__global__ void __launch_bounds__(kThreads, kBlocksPerSM) igg_halo_exchange_kernel(const __grid_constant__ KParams p) { halo_exchange_body<1>(p); }
+__global__ void __launch_bounds__(kThreads, kBlocksPerSM) igg_halo_exchange_kernel(const __grid_constant__ KParams p) { halo_exchange_body<1, false>(p); }
+// The same schedule with line-formatted staging (IGG_MODE_IPC_LL128): PUSH_LL / LOCAL / UNPACK_LL tiles.
+__global__ void __launch_bounds__(kThreads, kBlocksPerSM) igg_halo_exchange_ll128_kernel(const __grid_constant__ KParams p) { halo_exchange_body<1, true>(p); }
 }  // namespace
 
 int halo_kernel_max_coresident_blocks(int device) {
-    int per_sm = 0, sms = 0;
+    int per_sm = 0, per_sm_ll = 0, sms = 0;
     if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, igg_halo_exchange_kernel, kThreads, 0) != cudaSuccess) return -1;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm_ll, igg_halo_exchange_ll128_kernel, kThreads, 0) != cudaSuccess) return -1;
     if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device) != cudaSuccess) return -1;
-    return per_sm * sms;
+    return (per_sm < per_sm_ll ? per_sm : per_sm_ll) * sms;      // a grid that is co-resident for either kernel
 }
 
-int launch_halo_kernel(const KParams& p, int grid, void* stream) {
+int launch_halo_kernel(const KParams& p, int grid, void* stream, bool ll128) {
     // IGG_PDL=1 switches programmatic dependent launch on.  Measured (graph replay, cfg2): it hides launch latency for
     // tiny updates (y-faces only: 3.44 -> 2.77 us) but the early-scheduled next grid slows a full update down
     // (1 GPU 9.7 -> 12.3 us, 2 GPUs 15.6 -> 18.2 us), so plain stream order is the default.
@@ -312,7 +447,8 @@ int launch_halo_kernel(const KParams& p, int grid, void* stream) {
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
     cfg.numAttrs = pdl ? 1 : 0;
-    cudaError_t e = cudaLaunchKernelEx(&cfg, igg_halo_exchange_kernel, p);
+    cudaError_t e = ll128 ? cudaLaunchKernelEx(&cfg, igg_halo_exchange_ll128_kernel, p)
+                          : cudaLaunchKernelEx(&cfg, igg_halo_exchange_kernel, p);
     if (e == cudaSuccess) e = cudaGetLastError();
     if (e != cudaSuccess) return fail(IGG_ERR_CUDA, "halo kernel launch failed: %s", cudaGetErrorString(e));
     return IGG_OK;

@@ -87,8 +87,9 @@ struct Plan {
     int                      dims_mask = 0;          // bit d set: dimension d (0..2) is updated
     std::vector<igg_plan_op> ops;                    // PUSH ops, then LOCAL, then UNPACK
     std::vector<TileRec>     tiles;
+    bool     ll128 = false;                          // tiles are kOpPushLL / LOCAL / kOpUnpackLL
     int32_t  n_push_tiles = 0;
-    uint32_t n_flags = 0;                            // arrival flags this plan uses (must be <= kMaxFlags)
+    uint32_t n_flags = 0;                           // arrival flags this plan uses (must be <= kMaxFlags)
     uint32_t active_mask = 0;                        // bit o set: this plan exchanges with the neighbour at offset o
     int32_t  peer[IGG_NOFFSETS];                     // rank at offset o (or -1)
     int64_t  staging_bytes = 0;                      // bytes of one staging half this plan needs
@@ -115,8 +116,9 @@ int check_fields(const igg_grid_desc& g, int nfields, const igg_field* fields);
 int ranges(const igg_grid_desc& g, const igg_field& f, int n, int dim, bool send, int64_t out[6]);
 // Builds ops + tiles for this rank.  Pure host code.  `host_lines[i]` != 0 (optional): field i lives in page-locked
 // host memory on a 64-byte boundary, so its periodic x self-wrap may be emitted as kOpWrapLines tiles.
+// `ll128`: emit PUSH / UNPACK as kOpPushLL / kOpUnpackLL tiles over line-formatted staging (IGG_MODE_IPC_LL128).
 int build_plan(const igg_grid_desc& g, int nfields, const igg_field* fields, int dims_mask, Plan& plan,
-               const uint8_t* host_lines = nullptr);
+               const uint8_t* host_lines = nullptr, bool ll128 = false);
 void build_block_copy_tiles(int64_t el, const int64_t ext[3], const int64_t dst_size[2], const int64_t dst_origin[3],
                             int64_t src_align, int64_t dst_align, std::vector<TileRec>& tiles);
 constexpr int kOpCopy = 3;   // internal tile kind: field[t.field] -> push_base[t.nbr], no signalling (gather!, NCCL pack)
@@ -129,6 +131,19 @@ constexpr int kOpCopyIn = 4; // internal tile kind: unpack_base[t.nbr] -> field[
 // dst_sy = halo width in bytes, dst_sz = overlap in bytes (<= 64); ncols = 8 lanes per row.
 constexpr int kOpWrapLines = 5;
 constexpr int kWrapRowsPerTile = 128;
+// IGG_MODE_IPC_LL128: PUSH / UNPACK through line-formatted staging.  A staging slot of n payload bytes is
+// ceil(n / 120) lines of 128 bytes: bytes [0,120) payload (the box in column-major order, as a stream of W-byte
+// words, W = widest power of two <= 8 that divides element size and alignments), bytes [120,128) the epoch of the
+// call that wrote the line.  Eight lanes own a line (16 bytes each; lane 7: 8 payload bytes + the epoch); a warp
+// stores / loads 4 lines per instruction, and each line travels as one 128-byte transaction (what NCCL's LL128
+// protocol relies on over NVLink).
+// TileRec use: the FIELD side of either kind is in src_off / src_sy / src_sz / ny and ncols = bytes of a merged row;
+// row0 = first line of the tile inside the slot, nrows = lines in the tile; dst_off = byte offset of the slot in a
+// staging half, dst_sy = payload bytes of the slot; vec_log2 = log2(W); nbr as for PUSH / UNPACK.
+constexpr int kOpPushLL = 6;
+constexpr int kOpUnpackLL = 7;
+constexpr int kLinePayload = 120;
+constexpr int kLinesPerTile = 64;
 int build_dim_phase(const igg_grid_desc& g, int nfields, const igg_field* fields, int d, std::vector<TileRec>& pack,
                     std::vector<TileRec>& unpack, int64_t bytes[2]);
 // dims=(...) keyword -> bit mask of updated dimensions (NULL / empty = all three).
@@ -146,7 +161,7 @@ int  nccl_phase(NcclPath* np, const igg_grid_desc& g, int nfields, const igg_fie
 
 // ---- kernel launcher (halo_kernel.cu) ----------------------------------------------------------------------
 int  halo_kernel_max_coresident_blocks(int device);     // occupancy * SM count
-int  launch_halo_kernel(const KParams& p, int grid, void* stream);
+int  launch_halo_kernel(const KParams& p, int grid, void* stream, bool ll128 = false);
 const char* halo_kernel_name();
 // kOpWrapLines tiles (host-resident fields), one block per tile, stream-ordered.
 int  launch_wrap_lines_kernel(const TileRec* d_tiles, int n_tiles, void* const* fields, int nfields, void* stream);

@@ -247,7 +247,8 @@ void lower_op(const igg_field& f, int field_idx, int kind, int nbr, const Box& s
 }  // namespace
 
 int build_plan(const igg_grid_desc& g, int nfields, const igg_field* fields, int dims_mask, Plan& plan,
-               const uint8_t* host_lines) {
+               const uint8_t* host_lines, bool ll128) {
+    plan.ll128 = ll128;
     int rc = check_grid(g);
     if (rc) return rc;
     rc = check_fields(g, nfields, fields);
@@ -303,6 +304,10 @@ int build_plan(const igg_grid_desc& g, int nfields, const igg_field* fields, int
             }
             if (!ok || !remote) continue;       // self-wraps copy inside the array and need no staging slot
             slot_off[(size_t)oi * nfields + i] = total;
+            if (ll128) {                        // lines of 120 payload bytes + 8 flag bytes; no separate flags
+                total += (n + kLinePayload - 1) / kLinePayload * 128;
+                continue;
+            }
             total += round_up(n, 128);
             slot_flag[(size_t)oi * nfields + i] = nflags;
             slot_nflag[(size_t)oi * nfields + i] = (uint32_t)(2 * ((n + kTileBytes - 1) / kTileBytes) + 1);
@@ -412,6 +417,51 @@ int build_plan(const igg_grid_desc& g, int nfields, const igg_field* fields, int
             } else {
                 op.kind = IGG_OP_PUSH;
                 op.staging_off = slot_off[(size_t)opposite_index(oi) * nfields + i];
+                if (ll128) {
+                    // Same boxes, line-formatted staging: the op descriptions keep the field-side geometry (merged
+                    // rows and strides); the tiles are runs of staging lines.
+                    auto emit_ll = [&](int kind, int64_t foff, int64_t fsy, int64_t fsz, const igg_plan_op& d, std::vector<TileRec>& out) {
+                        const int64_t nlines = (d.nbytes + kLinePayload - 1) / kLinePayload;
+                        int wlog = 0;
+                        while ((2 << wlog) <= std::min<int64_t>(8, d.vec_bytes)) ++wlog;
+                        for (int64_t l0 = 0; l0 < nlines; l0 += kLinesPerTile) {
+                            TileRec t;
+                            std::memset(&t, 0, sizeof(t));
+                            t.src_off = foff; t.src_sy = fsy; t.src_sz = fsz;
+                            t.ny = (uint32_t)d.ny; t.ncols = (uint32_t)d.row_bytes;
+                            t.row0 = (uint32_t)l0; t.nrows = (uint32_t)std::min<int64_t>(kLinesPerTile, nlines - l0);
+                            t.dst_off = d.staging_off; t.dst_sy = d.nbytes;
+                            t.field = (uint16_t)i; t.vec_log2 = (uint8_t)wlog; t.kind = (uint8_t)kind; t.nbr = (uint8_t)oi;
+                            out.push_back(t);
+                        }
+                    };
+                    std::vector<TileRec> unused;
+                    lower_op(f, i, IGG_OP_PUSH, oi, snd, snd, true, false, op.staging_off, op, unused);
+                    if (op.row_bytes >= (int64_t)1 << 32)
+                        return fail(IGG_ERR_ARG, "update_halo: a contiguous run of 4 GiB or more is not supported in LL128 mode.");
+                    op.flag_base = -1;
+                    emit_ll(kOpPushLL, op.src_off, op.src_sy, op.src_sz, op, tpush);
+                    push.push_back(op);
+                    plan.active_mask |= 1u << oi;
+                    plan.bytes_sent += op.nbytes;
+
+                    igg_plan_op up;
+                    std::memset(&up, 0, sizeof(up));
+                    up.kind = IGG_OP_UNPACK;
+                    up.field = i;
+                    up.peer = (int32_t)peer;
+                    for (int d = 0; d < 3; ++d) {
+                        up.offset[d] = o[d];
+                        up.dst_lo[d] = rcv_mine.lo[d]; up.dst_hi[d] = rcv_mine.hi[d];
+                    }
+                    up.staging_off = slot_off[(size_t)oi * nfields + i];
+                    up.flag_base = -1;
+                    unused.clear();
+                    lower_op(f, i, IGG_OP_UNPACK, oi, rcv_mine, rcv_mine, false, true, up.staging_off, up, unused);
+                    emit_ll(kOpUnpackLL, up.dst_off, up.dst_sy, up.dst_sz, up, tunpack);
+                    unpack.push_back(up);
+                    continue;
+                }
                 const size_t first_push = tpush.size();
                 lower_op(f, i, IGG_OP_PUSH, oi, snd, snd, true, false, op.staging_off, op, tpush);
                 if (tpush.size() - first_push > slot_nflag[(size_t)opposite_index(oi) * nfields + i])
@@ -547,6 +597,25 @@ int igg_plan_describe(const igg_grid_desc* desc, int nfields, const igg_field* f
     if (ops_out) {
         if (ops_cap < (int)plan.ops.size()) return igg::fail(IGG_ERR_ARG, "igg_plan_describe: ops_cap too small (need %d).", (int)plan.ops.size());
         std::memcpy(ops_out, plan.ops.data(), plan.ops.size() * sizeof(igg_plan_op));
+    }
+    return IGG_OK;
+}
+
+int igg_plan_tiles(const igg_grid_desc* desc, int nfields, const igg_field* fields, const int* dims_order, int ndims_order,
+                   int mode, void* tiles_out, int tiles_cap, int* ntiles_out, int64_t* staging_bytes_out) {
+    if (!desc || !fields || !ntiles_out) return igg::fail(IGG_ERR_ARG, "igg_plan_tiles: NULL argument.");
+    if (mode != IGG_MODE_IPC_1PHASE && mode != IGG_MODE_IPC_LL128) return igg::fail(IGG_ERR_ARG, "igg_plan_tiles: mode must be an IPC mode.");
+    int mask;
+    int rc = igg::dims_mask_from_order(dims_order, ndims_order, &mask);
+    if (rc) return rc;
+    igg::Plan plan;
+    rc = igg::build_plan(*desc, nfields, fields, mask, plan, nullptr, mode == IGG_MODE_IPC_LL128);
+    if (rc) return rc;
+    *ntiles_out = (int)plan.tiles.size();
+    if (staging_bytes_out) *staging_bytes_out = plan.staging_bytes;
+    if (tiles_out) {
+        if (tiles_cap < (int)plan.tiles.size()) return igg::fail(IGG_ERR_ARG, "igg_plan_tiles: tiles_cap too small (need %d).", (int)plan.tiles.size());
+        std::memcpy(tiles_out, plan.tiles.data(), plan.tiles.size() * sizeof(igg::TileRec));
     }
     return IGG_OK;
 }

@@ -15,7 +15,7 @@ IGG_OK = 0
 IGG_ERR_ARG, IGG_ERR_CUDA, IGG_ERR_STATE, IGG_ERR_FIELDS, IGG_ERR_IPC = -1, -2, -3, -4, -5
 IGG_ERR_NCCL, IGG_ERR_TIMEOUT, IGG_ERR_UNSUPPORTED, IGG_ERR_GRID = -6, -7, -8, -9
 IGG_SYNC, IGG_ASYNC = 0, 1
-IGG_MODE_IPC_1PHASE, IGG_MODE_NCCL_3PHASE = 0, 1
+IGG_MODE_IPC_1PHASE, IGG_MODE_NCCL_3PHASE, IGG_MODE_IPC_LL128 = 0, 1, 2
 IGG_OP_PUSH, IGG_OP_LOCAL, IGG_OP_UNPACK = 0, 1, 2
 IGG_PROC_NULL = -1
 IGG_MAX_FIELDS = 32
@@ -90,6 +90,7 @@ def load():
         "igg_recvranges": (C.c_int, [gd, fp, i32, i32, i64p]),
         "igg_check_fields": (C.c_int, [gd, i32, fp]),
         "igg_plan_describe": (C.c_int, [gd, i32, fp, i32p, i32, C.POINTER(PlanOp), i32, i32p, i64p]),
+        "igg_plan_tiles": (C.c_int, [gd, i32, fp, i32p, i32, i32, vp, i32, i32p, i64p]),
         "igg_ctrl_selftest_create": (C.c_int, [i32, i32, C.c_char_p, C.POINTER(vp)]),
         "igg_ctrl_selftest_run": (C.c_int, [vp, i32, i32, C.c_char_p, i32]),
         "igg_debug_state": (C.c_int, [vp, C.POINTER(C.c_uint64)]),
@@ -109,7 +110,7 @@ def load():
 DECLARED_SYMBOLS = [
     "igg_version", "igg_last_error", "igg_create", "igg_destroy", "igg_bootstrap_size", "igg_bootstrap_export",
     "igg_bootstrap_import", "igg_update_halo", "igg_update_halo_noalloc", "igg_noalloc_scratch_bytes", "igg_set_mode", "igg_nccl_unique_id_size", "igg_nccl_get_unique_id",
-    "igg_nccl_init", "igg_gather", "igg_diffusion3d_step", "igg_sendranges", "igg_recvranges", "igg_check_fields", "igg_plan_describe",
+    "igg_nccl_init", "igg_gather", "igg_diffusion3d_step", "igg_sendranges", "igg_recvranges", "igg_check_fields", "igg_plan_describe", "igg_plan_tiles",
     "igg_ctrl_selftest_create", "igg_ctrl_selftest_run", "igg_debug_state", "igg_trace_enable", "igg_trace_read",
     "igg_launch_count", "igg_kernel_name",
 ]
@@ -155,3 +156,26 @@ def plan_describe(desc: GridDesc, fields, dims=None):
     ops = (PlanOp * max(1, n.value))()
     check(lib.igg_plan_describe(C.byref(desc), len(fields), arr, dptr, nd, ops, n.value, C.byref(n), C.byref(stg)))
     return [ops[i] for i in range(n.value)], stg.value
+
+
+class TileRec(C.Structure):
+    """Mirror of struct TileRec (csrc/igg_internal.h), 80 bytes; what one thread block iteration works on."""
+    _fields_ = [("src_off", C.c_int64), ("dst_off", C.c_int64), ("src_sy", C.c_int64), ("src_sz", C.c_int64),
+                ("dst_sy", C.c_int64), ("dst_sz", C.c_int64), ("row0", C.c_uint32), ("nrows", C.c_uint32),
+                ("ncols", C.c_uint32), ("ny", C.c_uint32), ("field", C.c_uint16), ("vec_log2", C.c_uint8),
+                ("kind", C.c_uint8), ("nbr", C.c_uint8), ("pad", C.c_uint8 * 3), ("flag_idx", C.c_uint32),
+                ("pad2", C.c_uint32)]
+
+
+def plan_tiles(desc: GridDesc, fields, dims=None, mode=IGG_MODE_IPC_1PHASE):
+    """Returns (list[TileRec], staging_bytes): the tile table of the exchange kernel of `mode` (host only)."""
+    assert C.sizeof(TileRec) == 80
+    lib = load()
+    arr = (Field * len(fields))(*fields)
+    n = C.c_int(0)
+    stg = C.c_int64(0)
+    dptr, nd = (None, 0) if dims is None else ((C.c_int * len(dims))(*dims), len(dims))
+    check(lib.igg_plan_tiles(C.byref(desc), len(fields), arr, dptr, nd, mode, None, 0, C.byref(n), C.byref(stg)))
+    tiles = (TileRec * max(1, n.value))()
+    check(lib.igg_plan_tiles(C.byref(desc), len(fields), arr, dptr, nd, mode, tiles, n.value, C.byref(n), C.byref(stg)))
+    return [tiles[i] for i in range(n.value)], stg.value

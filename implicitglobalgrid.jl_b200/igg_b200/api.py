@@ -327,14 +327,16 @@ def update_halo(*A, dims=(3, 1, 2), stream=None, blocking=True):
 
 def set_exchange_mode(mode):
     """Selects how update_halo moves data between ranks: "ipc" (default: one fused kernel, peer stores over NVLink)
-    or "nccl" (comparison path: per-dimension pack kernel, grouped ncclSend/ncclRecv, unpack kernel).  Collective."""
+    "ll128" (the same fused kernel, but every 128-byte line of staged data carries its own arrival flag, so there is
+    no release fence and no separate flag), or "nccl" (comparison path: per-dimension pack kernel, grouped
+    ncclSend/ncclRecv, unpack kernel).  Collective."""
     g = global_grid()
     lib = L.load()
-    if mode == "ipc":
-        L.check(lib.igg_set_mode(g.ctx, L.IGG_MODE_IPC_1PHASE))
+    if mode in ("ipc", "ll128"):
+        L.check(lib.igg_set_mode(g.ctx, L.IGG_MODE_IPC_1PHASE if mode == "ipc" else L.IGG_MODE_IPC_LL128))
         return
     if mode != "nccl":
-        raise ArgumentError(f"unknown exchange mode {mode!r} (use 'ipc' or 'nccl')")
+        raise ArgumentError(f"unknown exchange mode {mode!r} (use 'ipc', 'll128' or 'nccl')")
     if g.nprocs > 1:
         n = lib.igg_nccl_unique_id_size()
         buf = C.create_string_buffer(n)

@@ -50,8 +50,13 @@ enum igg_flags {
 enum igg_mode {
     IGG_MODE_IPC_1PHASE = 0,  /* default: one fused kernel, all 26 neighbour regions in one phase, peer stores over
                                  NVLink + device-side flags */
-    IGG_MODE_NCCL_3PHASE = 1  /* comparison path: pack kernel -> grouped ncclSend/ncclRecv -> unpack kernel, one
+    IGG_MODE_NCCL_3PHASE = 1, /* comparison path: pack kernel -> grouped ncclSend/ncclRecv -> unpack kernel, one
                                  phase per dimension in the reference's order (ref: src/update_halo.jl:51-88) */
+    IGG_MODE_IPC_LL128 = 2    /* like IGG_MODE_IPC_1PHASE, but the staged data carries its own arrival flags: every
+                                 128-byte line of staging is 120 bytes of payload + the call's 8-byte epoch, stored by
+                                 one warp instruction, so the sender needs neither a release fence nor a separate flag
+                                 and the receiver unpacks each line as it lands.  Selecting it (or leaving it) is
+                                 collective: all ranks call igg_set_mode together; it clears the staging memory. */
 };
 
 /* Mirror of the reference's GlobalGrid (ref: src/shared.jl:58-81), reduced to what the halo path reads.
@@ -199,6 +204,13 @@ typedef struct igg_plan_op {
 int igg_plan_describe(const igg_grid_desc* desc, int nfields, const igg_field* fields,
                       const int* dims_order, int ndims_order,
                       igg_plan_op* ops_out, int ops_cap, int* nops_out, int64_t* staging_bytes_out);
+/* The tile table the exchange kernel of `mode` (IGG_MODE_IPC_1PHASE or IGG_MODE_IPC_LL128) would walk for this call
+ * on this rank: `*ntiles_out` records of 80 bytes each (layout: struct TileRec in csrc/igg_internal.h; PUSH tiles
+ * first, then LOCAL, then UNPACK).  Host only, for tests that execute the table without a GPU.  No reference
+ * counterpart. */
+int igg_plan_tiles(const igg_grid_desc* desc, int nfields, const igg_field* fields,
+                   const int* dims_order, int ndims_order, int mode,
+                   void* tiles_out, int tiles_cap, int* ntiles_out, int64_t* staging_bytes_out);
 
 /* Control-plane self test (host only).  After the bootstrap the library talks between ranks through one POSIX
  * shared-memory mailbox per rank (segment re-allocation hand-shakes, the barrier of gather!) -- the places where the

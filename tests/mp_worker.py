@@ -22,6 +22,9 @@ import igg_b200 as igg  # noqa: E402
 from oracle import igg_oracle as O  # noqa: E402
 
 TDT = {1: torch.uint8, 2: torch.int16, 4: torch.int32, 8: torch.int64}
+# The IPC protocol under test: contexts start in the one IGG_MODE names ("ll128", else the fence protocol); after a
+# detour through the NCCL comparison path the worker goes back to the same one.
+IPC_MODE = "ll128" if os.environ.get("IGG_MODE") == "ll128" else "ipc"
 
 
 def case_list(n):
@@ -95,7 +98,7 @@ def main():
                 load(tn, rep)
                 igg.update_halo(*[(t, hw) for t, hw in zip(tn, hws_)], dims=dims, blocking=(rep == 0))
             torch.cuda.synchronize()
-            igg.set_exchange_mode("ipc")
+            igg.set_exchange_mode(IPC_MODE)
         else:
             tn = None
         ts = [igg.from_numpy(a) for a in base]
@@ -183,7 +186,7 @@ def main():
     igg.update_halo(a)
     igg.set_exchange_mode("nccl")
     igg.update_halo(b)
-    igg.set_exchange_mode("ipc")
+    igg.set_exchange_mode(IPC_MODE)
     torch.cuda.synchronize()
     if not torch.equal(a, b):
         ok = False

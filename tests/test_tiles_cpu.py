@@ -1,0 +1,148 @@
+"""Tile tables of the exchange kernels, executed on the CPU (no GPU needed).
+
+`igg_plan_tiles` returns the very records the CUDA kernels walk (struct TileRec).  Here every simulated rank's table
+is executed with numpy exactly as the kernels address memory -- fence mode (PUSH / LOCAL / UNPACK tiles of rows and
+columns) and LL128 mode (PUSH_LL / UNPACK_LL tiles over line-formatted staging: 120 payload bytes + 8-byte epoch per
+128-byte line) -- and the fields must come out bit-identical to the oracle, and to the committed golden vectors.
+This pins the host side of IGG_MODE_IPC_LL128 (slot layout, line numbering, field-side geometry, word width)."""
+import numpy as np
+import pytest
+
+import golden_cases as G
+from igg_b200 import _lib as L
+from oracle import igg_oracle as O
+from test_plan_vs_oracle import desc_of, flat_bytes, rand_field
+
+PUSH, LOCAL, UNPACK, PUSH_LL, UNPACK_LL = 0, 1, 2, 6, 7
+LINE, PAYLOAD = 128, 120
+OFFSETS = [(ox, oy, oz) for oz in (-1, 0, 1) for oy in (-1, 0, 1) for ox in (-1, 0, 1)]   # index = (ox+1)+3(oy+1)+9(oz+1)
+
+
+def peer_of(g, nbr):
+    o = OFFSETS[nbr]
+    c = []
+    for d in range(3):
+        v = g.coords[d] + o[d]
+        if g.periods[d]:
+            v %= g.dims[d]
+        assert 0 <= v < g.dims[d]
+        c.append(v)
+    return (c[0] * g.dims[1] + c[1]) * g.dims[2] + c[2]
+
+
+def copy_rows(t, src, dst):
+    """copy_tile of the kernel: nrows rows from row0, ncols words of (1 << vec_log2) bytes each."""
+    nb = t.ncols << t.vec_log2
+    for r in range(t.nrows):
+        row = t.row0 + r
+        y, z = row % t.ny, row // t.ny
+        s = t.src_off + y * t.src_sy + z * t.src_sz
+        d = t.dst_off + y * t.dst_sy + z * t.dst_sz
+        dst[d:d + nb] = src[s:s + nb]
+
+
+def box_offset(t, pb):
+    """box_seek of the kernel: payload byte pb -> byte offset in the field."""
+    r, c = divmod(pb, t.ncols)
+    z, y = divmod(r, t.ny)
+    return t.src_off + y * t.src_sy + z * t.src_sz + c
+
+
+def run_tables(grids, fields_per_rank, hws, dims, mode, epoch=7):
+    n = len(grids)
+    mem = [[flat_bytes(A) for A in fr] for fr in fields_per_rank]
+    tables, stagings = [], []
+    for r, g in enumerate(grids):
+        cf = [L.make_field(0x10000 * (i + 1), A.shape, hws[i], A.dtype.itemsize) for i, A in enumerate(fields_per_rank[r])]
+        tiles, stg = L.plan_tiles(desc_of(g), cf, dims, mode)
+        tables.append(tiles)
+        stagings.append(np.full(max(stg, 1), 0xEE, dtype=np.uint8))
+    kinds = {t.kind for tb in tables for t in tb}
+    assert kinds <= ({PUSH_LL, LOCAL, UNPACK_LL} if mode == L.IGG_MODE_IPC_LL128 else {PUSH, LOCAL, UNPACK})
+    ep = np.frombuffer(np.uint64(epoch).tobytes(), dtype=np.uint8)
+    for r, g in enumerate(grids):                       # everything that does not wait
+        order = [t.kind for t in tables[r]]
+        assert order == sorted(order, key=lambda k: {PUSH: 0, PUSH_LL: 0, LOCAL: 1, UNPACK: 2, UNPACK_LL: 2}[k])
+        for t in tables[r]:
+            if t.kind == PUSH:
+                copy_rows(t, mem[r][t.field], stagings[peer_of(g, t.nbr)])
+            elif t.kind == LOCAL:
+                copy_rows(t, mem[r][t.field], mem[r][t.field])
+            elif t.kind == PUSH_LL:
+                W, nbytes, stg = 1 << t.vec_log2, t.dst_sy, stagings[peer_of(g, t.nbr)]
+                assert t.ncols % W == 0 and nbytes % W == 0 and t.dst_off % LINE == 0
+                for line in range(t.row0, t.row0 + t.nrows):
+                    base = t.dst_off + line * LINE
+                    for pb in range(line * PAYLOAD, min(line * PAYLOAD + PAYLOAD, nbytes), W):
+                        s = box_offset(t, pb)
+                        stg[base + pb - line * PAYLOAD: base + pb - line * PAYLOAD + W] = mem[r][t.field][s:s + W]
+                    stg[base + PAYLOAD: base + LINE] = ep
+    for r, g in enumerate(grids):                       # everything that waits for a neighbour
+        for t in tables[r]:
+            if t.kind == UNPACK:
+                copy_rows(t, stagings[r], mem[r][t.field])
+            elif t.kind == UNPACK_LL:
+                W, nbytes, stg = 1 << t.vec_log2, t.dst_sy, stagings[r]
+                for line in range(t.row0, t.row0 + t.nrows):
+                    base = t.dst_off + line * LINE
+                    assert np.array_equal(stg[base + PAYLOAD: base + LINE], ep), "line was never pushed"
+                    for pb in range(line * PAYLOAD, min(line * PAYLOAD + PAYLOAD, nbytes), W):
+                        d = box_offset(t, pb)
+                        mem[r][t.field][d:d + W] = stg[base + pb - line * PAYLOAD: base + pb - line * PAYLOAD + W]
+    # every line of every LL slot that is read was written exactly once per call: count lines
+    if mode == L.IGG_MODE_IPC_LL128:
+        for r, g in enumerate(grids):
+            pushed = sum(t.nrows for q, gq in enumerate(grids) for t in tables[q] if t.kind == PUSH_LL and peer_of(gq, t.nbr) == r)
+            assert pushed == sum(t.nrows for t in tables[r] if t.kind == UNPACK_LL)
+
+
+CASES = [
+    # nprocs, grid, kwargs, shapes, per-field halowidths or None, elsize, dims
+    (2, (13, 9, 10), dict(periodx=1, periody=1, periodz=1), [(13, 9, 10)], None, 8, (3, 1, 2)),
+    (4, (13, 9, 10), dict(), [(13, 9, 10), (14, 9, 10), (13, 10, 10), (13, 9, 11)], None, 8, (3, 1, 2)),
+    (8, (13, 9, 10), dict(periodx=1, periodz=1, overlaps=(4, 2, 3), halowidths=(2, 1, 1)),
+     [(13, 9, 10), (14, 9, 10), (12, 11, 11)], None, 4, (3, 1, 2)),
+    (8, (13, 9, 10), dict(periodx=1, periody=1, periodz=1, overlaps=(4, 4, 4), halowidths=(2, 2, 2)),
+     [(13, 9, 10), (13, 9, 10), (14, 9, 10)], [(2, 2, 2), (1, 1, 2), (2, 1, 1)], 8, (3, 1, 2)),
+    (8, (40, 30, 1), dict(periodx=1, periody=1), [(40, 30), (41, 30)], None, 8, (3, 1, 2)),
+    (4, (64, 1, 1), dict(periodx=1), [(64,), (65,)], None, 4, (3, 1, 2)),
+    (8, (40, 36, 34), dict(periodx=1, periody=1, periodz=1), [(40, 36, 34)], None, 8, (3, 1, 2)),      # several tiles per slot
+    (2, (13, 9, 10), dict(periody=1, overlaps=(6, 4, 4), halowidths=(3, 1, 2)), [(13, 9, 10), (13, 9, 11)], None, 2, (1, 3)),
+    (8, (13, 9, 10), dict(periodx=1, periody=1, periodz=1), [(13, 9, 10)], None, 1, (2, 1)),
+    (8, (13, 9, 10), dict(periodx=1, periody=1, periodz=1), [(13, 9, 10), (14, 9, 10)], None, 16, (3, 1, 2)),
+    (4, (13, 9, 10), dict(periodx=1, periody=1, periodz=1), [(13, 9, 10)], None, 12, (3, 1, 2)),       # W = 4 < element
+]
+
+
+def struct_field(shape, elsize, seed):
+    rng = np.random.default_rng(seed)
+    return np.asfortranarray(rng.integers(0, 256, size=tuple(shape) + (elsize,), dtype=np.uint8).view(f"V{elsize}")[..., 0])
+
+
+@pytest.mark.parametrize("mode", [L.IGG_MODE_IPC_1PHASE, L.IGG_MODE_IPC_LL128], ids=["fence", "ll128"])
+@pytest.mark.parametrize("case", CASES, ids=[f"c{i}" for i in range(len(CASES))])
+def test_tile_tables_match_oracle(case, mode):
+    nprocs, gsz, kw, shapes, hws, elsize, dims = case
+    grids = O.make_grids(nprocs, *gsz, **kw)
+    hws = hws or [grids[0].halowidths] * len(shapes)
+    mk = struct_field if elsize == 12 else rand_field
+    base = [[mk(s, elsize, 1000 * r + 10 * i + 3) for i, s in enumerate(shapes)] for r in range(nprocs)]
+    want = [[a.copy(order="F") for a in fr] for fr in base]
+    O.update_halo(grids, [[(a, hws[i]) for i, a in enumerate(fr)] for fr in want], dims=dims)
+    got = [[a.copy(order="F") for a in fr] for fr in base]
+    run_tables(grids, got, hws, dims, mode)
+    for r in range(nprocs):
+        for i in range(len(shapes)):
+            assert np.array_equal(flat_bytes(got[r][i]), flat_bytes(want[r][i])), (r, i)
+
+
+@pytest.mark.parametrize("mode", [L.IGG_MODE_IPC_1PHASE, L.IGG_MODE_IPC_LL128], ids=["fence", "ll128"])
+@pytest.mark.parametrize("ci,case", [(i, c) for i, c in G.cases() if c["nprocs"] > 1], ids=[c["name"] for _, c in G.cases() if c["nprocs"] > 1])
+def test_tile_tables_match_golden(ci, case, mode):
+    grids = O.make_grids(case["nprocs"], *case["grid"], **G.kwargs(case))      # grid descriptions only
+    hws = G.halowidths(case, grids[0].halowidths)
+    fields = [G.arrays(ci, r, "in") for r in range(case["nprocs"])]
+    run_tables(grids, fields, hws, tuple(case["dims"]), mode)
+    for r in range(case["nprocs"]):
+        for a, w in zip(fields[r], G.arrays(ci, r, "out")):
+            assert np.array_equal(a, w), (case["name"], r)
