@@ -386,6 +386,8 @@ def run_b200(args):
         "host_issue_us_per_call": host_issue_us,
         "clocks": clocks,
         "kernel": lib.igg_kernel_name().decode(),
+        "protocol": "fence (release fence + flag per 8-KiB tile)" if os.environ.get("IGG_MODE") in ("fence", "ipc")
+                    else "ll128 (120 payload bytes + 8-byte epoch per 128-byte staging line; default)",
     }
     print(json.dumps(line))
     return 0

@@ -77,7 +77,7 @@ using namespace igg;
 struct igg_ctx {
     igg_grid_desc g;
     int device = 0;
-    int mode = IGG_MODE_IPC_1PHASE;
+    int mode = IGG_MODE_IPC_LL128;              // default protocol (IGG_MODE=fence selects IGG_MODE_IPC_1PHASE)
     char* ctrl = nullptr;                       // device: flags at 0, counters at kCountersOff
     char* staging = nullptr;                    // device: two halves
     int64_t staging_half = 0;
@@ -309,7 +309,7 @@ int igg_create(const igg_grid_desc* desc, igg_ctx** out) {
     ctx->max_blocks = halo_kernel_max_coresident_blocks(ctx->device);
     if (ctx->max_blocks <= 0) return fail(IGG_ERR_CUDA, "occupancy query for the halo kernel failed (was the library built for sm_100a?): %s", cudaGetErrorString(cudaGetLastError()));
     if (const char* t = getenv("IGG_DEVICE_TIMEOUT_S")) ctx->timeout_ns = (unsigned long long)(atof(t) * 1e9);
-    // IGG_MODE=ll128 / fence: the IPC protocol a new context starts in (must be the same on every rank).
+    // IGG_MODE=fence / ll128: the IPC protocol a new context starts in (default ll128; the same on every rank).
     if (const char* m = getenv("IGG_MODE")) {
         if (!strcmp(m, "ll128")) ctx->mode = IGG_MODE_IPC_LL128;
         else if (!strcmp(m, "fence") || !strcmp(m, "ipc")) ctx->mode = IGG_MODE_IPC_1PHASE;
@@ -719,6 +719,11 @@ int igg_nccl_init(igg_ctx* ctx, const void* id) {
 }
 
 int64_t igg_launch_count(const igg_ctx* ctx) { return ctx ? ctx->launches : 0; }
-const char* igg_kernel_name(void) { return halo_kernel_name(); }
+const char* igg_kernel_name(void) {
+    // the kernel a new context launches: LL128 unless IGG_MODE selects the fence protocol (as in igg_create)
+    const char* m = getenv("IGG_MODE");
+    const bool fence = m && (!strcmp(m, "fence") || !strcmp(m, "ipc"));
+    return fence ? halo_kernel_name() : "igg_halo_exchange_ll128_kernel";
+}
 
 }  // extern "C"

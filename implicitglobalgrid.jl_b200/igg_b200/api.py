@@ -326,17 +326,20 @@ def update_halo(*A, dims=(3, 1, 2), stream=None, blocking=True):
 
 
 def set_exchange_mode(mode):
-    """Selects how update_halo moves data between ranks: "ipc" (default: one fused kernel, peer stores over NVLink)
-    "ll128" (the same fused kernel, but every 128-byte line of staged data carries its own arrival flag, so there is
-    no release fence and no separate flag), or "nccl" (comparison path: per-dimension pack kernel, grouped
-    ncclSend/ncclRecv, unpack kernel).  Collective."""
+    """Selects how update_halo moves data between ranks.  "ipc": the default (one fused kernel, peer stores over
+    NVLink, protocol "ll128" unless the environment says IGG_MODE=fence).  "ll128": every 128-byte line of staged data
+    carries its own arrival flag, so there is no release fence and no separate flag.  "fence": one release fence and
+    one arrival flag per 8-KiB tile.  "nccl": comparison path (per-dimension pack kernel, grouped ncclSend/ncclRecv,
+    unpack kernel).  Collective."""
     g = global_grid()
     lib = L.load()
-    if mode in ("ipc", "ll128"):
-        L.check(lib.igg_set_mode(g.ctx, L.IGG_MODE_IPC_1PHASE if mode == "ipc" else L.IGG_MODE_IPC_LL128))
+    if mode == "ipc":        # the protocol new contexts start in: LL128 unless the environment says IGG_MODE=fence
+        mode = "fence" if os.environ.get("IGG_MODE") in ("fence", "ipc") else "ll128"
+    if mode in ("fence", "ll128"):
+        L.check(lib.igg_set_mode(g.ctx, L.IGG_MODE_IPC_1PHASE if mode == "fence" else L.IGG_MODE_IPC_LL128))
         return
     if mode != "nccl":
-        raise ArgumentError(f"unknown exchange mode {mode!r} (use 'ipc', 'll128' or 'nccl')")
+        raise ArgumentError(f"unknown exchange mode {mode!r} (use 'ipc', 'fence', 'll128' or 'nccl')")
     if g.nprocs > 1:
         n = lib.igg_nccl_unique_id_size()
         buf = C.create_string_buffer(n)

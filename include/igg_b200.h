@@ -48,11 +48,12 @@ enum igg_flags {
 };
 
 enum igg_mode {
-    IGG_MODE_IPC_1PHASE = 0,  /* default: one fused kernel, all 26 neighbour regions in one phase, peer stores over
-                                 NVLink + device-side flags */
+    IGG_MODE_IPC_1PHASE = 0,  /* one fused kernel, all 26 neighbour regions in one phase, peer stores over NVLink, one
+                                 release fence + arrival flag per 8-KiB tile ("fence" protocol; env IGG_MODE=fence
+                                 makes new contexts start in it) */
     IGG_MODE_NCCL_3PHASE = 1, /* comparison path: pack kernel -> grouped ncclSend/ncclRecv -> unpack kernel, one
                                  phase per dimension in the reference's order (ref: src/update_halo.jl:51-88) */
-    IGG_MODE_IPC_LL128 = 2    /* like IGG_MODE_IPC_1PHASE, but the staged data carries its own arrival flags: every
+    IGG_MODE_IPC_LL128 = 2    /* DEFAULT.  Like IGG_MODE_IPC_1PHASE, but the staged data carries its own arrival flags: every
                                  128-byte line of staging is 120 bytes of payload + the call's 8-byte epoch, stored by
                                  one warp instruction, so the sender needs neither a release fence nor a separate flag
                                  and the receiver unpacks each line as it lands.  Selecting it (or leaving it) is
