@@ -270,6 +270,31 @@ def _c_fields(fields):
 _call_cache = {}
 
 
+def _cell_of(a):
+    """The CellArray inside an update_halo argument (bare, (A, halowidths) or {'A':.., 'halowidths':..}), or None."""
+    x = a["A"] if isinstance(a, dict) else (a[0] if isinstance(a, (tuple, list)) and len(a) == 2 else a)
+    return x if hasattr(x, "bitsarrays") else None
+
+
+def _extract_all(A):
+    """extract (ref: src/shared.jl:246-250): CellArray arguments become their bits arrays (B = 0: one field per cell
+    component; B = 1: one field of whole cells), with the halowidths the argument carried."""
+    if not any(_cell_of(a) is not None for a in A):
+        return A
+    out = []
+    for a in A:
+        c = _cell_of(a)
+        if c is None:
+            out.append(a)
+        elif isinstance(a, dict):
+            out.extend({"A": b, "halowidths": a["halowidths"]} for b in c.bitsarrays())
+        elif isinstance(a, (tuple, list)):
+            out.extend((b, a[1]) for b in c.bitsarrays())
+        else:
+            out.extend(c.bitsarrays())
+    return tuple(out)
+
+
 def _field_key(a):
     if isinstance(a, dict):
         t, hw = a["A"], tuple(a["halowidths"])
@@ -290,6 +315,7 @@ def update_halo(*A, dims=(3, 1, 2), stream=None, blocking=True):
     if g is None:
         check_initialized()
     lib = L.load()
+    A = _extract_all(A)
     try:
         key = (tuple(_field_key(a) for a in A), tuple(dims))
         prepared = _call_cache.get(key)
@@ -355,6 +381,7 @@ def prepare_update_halo(*A, dims=(3, 1, 2), stream=None, blocking=True):
     """Validates the arguments once and returns a zero-argument callable that performs `update_halo!(A...)` with
     minimal host overhead (one foreign call).  For time loops that update the same arrays every step.  The arrays
     must stay alive and in place; `stream` defaults to the stream current at preparation time."""
+    A = _extract_all(A)
     update_halo(*A, dims=dims, stream=stream, blocking=True)      # validates, builds the plan, warms the caches
     key = (tuple(_field_key(a) for a in A), tuple(dims))
     arr, nf, d, nd = _call_cache[key]
