@@ -93,6 +93,8 @@ struct igg_ctx {
     cudaStream_t last_stream = nullptr;
     cudaEvent_t last_event = nullptr;
     bool have_last = false;
+    cudaStream_t side_stream = nullptr;         // host-resident fields: the wrap-lines kernel runs beside the exchange
+    cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     unsigned long long timeout_ns = 20ull * 1000000000ull;
     struct PtrEntry { const void* user = nullptr; void* resolved = nullptr; bool host = false; };
     PtrEntry ptr_cache[64];
@@ -343,6 +345,9 @@ int igg_destroy(igg_ctx* ctx) {
     if (ctx->ctrl) cudaFree(ctx->ctrl);
     if (ctx->h_status) cudaFreeHost(ctx->h_status);
     if (ctx->last_event) cudaEventDestroy(ctx->last_event);
+    if (ctx->ev_fork) cudaEventDestroy(ctx->ev_fork);
+    if (ctx->ev_join) cudaEventDestroy(ctx->ev_join);
+    if (ctx->side_stream) cudaStreamDestroy(ctx->side_stream);
     ctx->cp.close();
     delete ctx;
     return IGG_OK;
@@ -419,13 +424,31 @@ static int launch_exchange(igg_ctx* ctx, int nfields, const igg_field* fields, i
     int rc;
     Plan* plan = find_or_build_plan(ctx, nfields, fields, dims_mask, host_lines, &rc);
     if (!plan) return rc;
+    bool join_side = false;
     if (!plan->wrap_tiles.empty()) {
         // Whole-line x self-wrap of host-resident fields: its own kernel, independent of the other tiles of the call.
+        // It runs before the exchange kernel on the caller's stream.  IGG_HOST_FORK=1 runs it beside the exchange
+        // kernel on a side stream instead (fork / join with events); measured SLOWER on cfg2 (e2e 674 vs 570 us: the
+        // two kernels fight over the same PCIe read tags), so it is off by default.
+        static const bool fork = std::getenv("IGG_HOST_FORK") && std::atoi(std::getenv("IGG_HOST_FORK")) == 1;
         void* ptrs[IGG_MAX_FIELDS];
         for (int i = 0; i < nfields; ++i) ptrs[i] = fields[i].ptr;
         order_after_previous(ctx, stream);
-        rc = launch_wrap_lines_kernel(plan->d_wrap_tiles, (int)plan->wrap_tiles.size(), ptrs, nfields, stream);
+        cudaStream_t ws = stream;
+        if (fork && !plan->tiles.empty()) {
+            if (!ctx->side_stream) {
+                CU(cudaStreamCreateWithFlags(&ctx->side_stream, cudaStreamNonBlocking));
+                CU(cudaEventCreateWithFlags(&ctx->ev_fork, cudaEventDisableTiming));
+                CU(cudaEventCreateWithFlags(&ctx->ev_join, cudaEventDisableTiming));
+            }
+            CU(cudaEventRecord(ctx->ev_fork, stream));
+            CU(cudaStreamWaitEvent(ctx->side_stream, ctx->ev_fork, 0));
+            ws = ctx->side_stream;
+            join_side = true;
+        }
+        rc = launch_wrap_lines_kernel(plan->d_wrap_tiles, (int)plan->wrap_tiles.size(), ptrs, nfields, ws);
         if (rc) return rc;
+        if (join_side) CU(cudaEventRecord(ctx->ev_join, ws));
         remember_launch(ctx, stream);
     }
     if (plan->tiles.empty()) return IGG_OK;                       // e.g. one rank, nothing periodic
@@ -464,6 +487,7 @@ static int launch_exchange(igg_ctx* ctx, int nfields, const igg_field* fields, i
         CU(cudaMemsetAsync(ctx->d_trace, 0, (size_t)ctx->max_blocks * 8 * sizeof(unsigned long long), stream));
     }
     rc = launch_halo_kernel(p, plan->grid, stream, plan->ll128);
+    if (join_side) CU(cudaStreamWaitEvent(stream, ctx->ev_join, 0));   // the call is complete when both kernels are
     if (rc) return rc;
     remember_launch(ctx, stream);
     return IGG_OK;
