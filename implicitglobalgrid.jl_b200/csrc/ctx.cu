@@ -93,6 +93,10 @@ struct igg_ctx {
     cudaStream_t last_stream = nullptr;
     cudaEvent_t last_event = nullptr;
     bool have_last = false;
+    // Staging / flag REGIONS, one per neighbour offset, identical on every rank (they only depend on the sequence of
+    // plans seen, and update_halo is collective): bytes inside one staging half and arrival-flag words.  Grow-only.
+    int64_t  region_cap[IGG_NOFFSETS] = {0}, region_off[IGG_NOFFSETS] = {0};
+    uint32_t flag_cap[IGG_NOFFSETS] = {0}, flag_off[IGG_NOFFSETS] = {0};
     cudaStream_t side_stream = nullptr;         // host-resident fields: the wrap-lines kernel runs beside the exchange
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     unsigned long long timeout_ns = 20ull * 1000000000ull;
@@ -184,6 +188,45 @@ static int grow_staging(igg_ctx* ctx, int64_t need_half) {
         rc = open_segment(ctx, ctx->peers[r], all[r].handle, all[r].ptr, ctx->peers[r].staging);
         if (rc) return rc;
         ctx->peers[r].staging.bytes = all[r].bytes;
+    }
+    return IGG_OK;
+}
+
+// Makes sure every neighbour offset's region (staging bytes, arrival flags) is large enough for `plan`.  Regions keep
+// their place from call to call, so data a neighbour pushes for one offset can never land on memory another
+// offset's neighbour writes or this rank still reads -- also when calls with different field sets or `dims=`
+// alternate and the ranks are not in lock-step.  Growing is collective and rare (first use of a bigger plan): every
+// rank reaches the same decision at the same call because the needs depend on the call's arguments only.
+static int ensure_layout(igg_ctx* ctx, const Plan& plan) {
+    bool grow = false;
+    for (int o = 0; o < IGG_NOFFSETS; ++o)
+        grow = grow || plan.region_need[o] > ctx->region_cap[o] || plan.flag_need[o] > ctx->flag_cap[o];
+    if (!grow) return IGG_OK;
+    int64_t cap[IGG_NOFFSETS], total = 0;
+    uint64_t fcap[IGG_NOFFSETS], ftotal = 0;
+    for (int o = 0; o < IGG_NOFFSETS; ++o) {
+        cap[o] = ctx->region_cap[o];
+        if (plan.region_need[o] > cap[o]) cap[o] = (plan.region_need[o] + plan.region_need[o] / 4 + 127) / 128 * 128;
+        fcap[o] = ctx->flag_cap[o];
+        if (plan.flag_need[o] > fcap[o]) fcap[o] = plan.flag_need[o];
+        total += cap[o];
+        ftotal += fcap[o];
+    }
+    if (ftotal > (uint64_t)kMaxFlags)
+        return fail(IGG_ERR_ARG, "update_halo: the calls made so far need %llu arrival flags, the control segment holds %d; "
+                    "use the LL128 protocol (default) or split the call.", (unsigned long long)ftotal, kMaxFlags);
+    int rc;
+    if (total > ctx->staging_half) {
+        rc = grow_staging(ctx, total);              // quiesces all ranks, re-allocates, re-maps
+    } else {
+        CU(cudaDeviceSynchronize());                // nobody exchanges while the regions move
+        rc = ctx->cp.barrier();
+    }
+    if (rc) return rc;
+    total = 0; ftotal = 0;
+    for (int o = 0; o < IGG_NOFFSETS; ++o) {
+        ctx->region_cap[o] = cap[o];  ctx->region_off[o] = total;          total += cap[o];
+        ctx->flag_cap[o] = (uint32_t)fcap[o]; ctx->flag_off[o] = (uint32_t)ftotal; ftotal += fcap[o];
     }
     return IGG_OK;
 }
@@ -455,8 +498,8 @@ static int launch_exchange(igg_ctx* ctx, int nfields, const igg_field* fields, i
     if (plan->n_flags > (uint32_t)kMaxFlags)
         return fail(IGG_ERR_ARG, "update_halo: this call needs %u arrival flags, the control segment holds %d; split the call.",
                     plan->n_flags, kMaxFlags);
-    if (plan->active_mask && plan->staging_bytes > ctx->staging_half) {
-        rc = grow_staging(ctx, plan->staging_bytes);
+    if (plan->active_mask) {
+        rc = ensure_layout(ctx, *plan);
         if (rc) return rc;
     }
 
@@ -475,10 +518,16 @@ static int launch_exchange(igg_ctx* ctx, int nfields, const igg_field* fields, i
     for (int oi = 0; oi < IGG_NOFFSETS; ++oi) {
         if (!((plan->active_mask >> oi) & 1u)) continue;
         const Peer& peer = ctx->peers[plan->peer[oi]];
-        p.push_base[oi] = peer.staging.ptr;
+        // The tiles carry offsets / flag numbers of the plan's own packed layout; shift every offset's base to that
+        // offset's region (same table on every rank).  What I push at offset oi lands in the receiver's region of
+        // the opposite offset.
+        const int ro = opposite_index(oi);
+        p.push_base[oi] = peer.staging.ptr + (ctx->region_off[ro] - plan->region_pack[ro]);
         p.push_half[oi] = peer.staging.bytes;
-        p.unpack_base[oi] = ctx->staging;
-        p.remote_flags[oi] = reinterpret_cast<unsigned long long*>(peer.ctrl.ptr + kFlagsOff);
+        p.unpack_base[oi] = ctx->staging + (ctx->region_off[oi] - plan->region_pack[oi]);
+        p.remote_flags[oi] = reinterpret_cast<unsigned long long*>(peer.ctrl.ptr + kFlagsOff) +
+                             ((long long)ctx->flag_off[ro] - (long long)plan->flag_pack[ro]);
+        p.local_flag_delta[oi] = (int32_t)((long long)ctx->flag_off[oi] - (long long)plan->flag_pack[oi]);
     }
     order_after_previous(ctx, stream);
     if (ctx->d_trace) {

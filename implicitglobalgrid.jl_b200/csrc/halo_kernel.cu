@@ -367,7 +367,7 @@ __device__ __forceinline__ void halo_exchange_body(const KParams& p) {
         } else if (!LL && t.kind == IGG_OP_UNPACK) {
             // Wait until the neighbour has flagged this very tile (it flags each tile right after storing it).
             if (threadIdx.x == 0) {
-                const unsigned long long* flag = p.local_flags + t.flag_idx;
+                const unsigned long long* flag = p.local_flags + ((long long)t.flag_idx + p.local_flag_delta[t.nbr]);
                 const unsigned long long want = s_epoch;
                 unsigned long long t0 = 0;
                 unsigned int spins = 0;

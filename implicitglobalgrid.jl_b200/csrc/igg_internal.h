@@ -60,6 +60,7 @@ struct KParams {
     long long unpack_half;                     // bytes of one staging half of mine
     unsigned long long* remote_flags[IGG_NOFFSETS];  // arrival-flag array in the control segment of the peer at offset o
     const unsigned long long* local_flags;     // my arrival-flag array (written by my neighbours)
+    int32_t  local_flag_delta[IGG_NOFFSETS];   // UNPACK tile of offset o waits for local_flags[flag_idx + delta[o]]
     // Exchange state in my control segment (NULL for launches that exchange nothing: gather!, NCCL pack/unpack).
     // It lives on the device so that the launch parameters do not change from call to call and an update_halo call
     // can be captured into a CUDA graph and replayed: the kernel derives this call's epoch (flag value) and each
@@ -93,6 +94,13 @@ struct Plan {
     uint32_t active_mask = 0;                        // bit o set: this plan exchanges with the neighbour at offset o
     int32_t  peer[IGG_NOFFSETS];                     // rank at offset o (or -1)
     int64_t  staging_bytes = 0;                      // bytes of one staging half this plan needs
+    // Per neighbour offset o: where this plan's slots / flags of offset o start when the offsets are packed one after
+    // the other (the numbers the tiles carry), and how much offset o needs.  At run time every offset has a REGION of
+    // its own whose position does not depend on the plan (igg_ctx::region_off / flag_off), and the launch shifts each
+    // offset's base pointer by (region_off[o] - region_pack[o]): memory an offset's neighbour writes is then never
+    // shared with another offset's neighbour, whatever sequence of plans (field sets, dims=) the caller runs.
+    int64_t  region_pack[IGG_NOFFSETS] = {0}, region_need[IGG_NOFFSETS] = {0};
+    uint32_t flag_pack[IGG_NOFFSETS] = {0}, flag_need[IGG_NOFFSETS] = {0};
     int64_t  bytes_sent = 0;                         // algorithmic halo bytes this rank sends (local + remote)
     // device copy (owned by the context)
     TileRec* d_tiles = nullptr;

@@ -291,8 +291,17 @@ int build_plan(const igg_grid_desc& g, int nfields, const igg_field* fields, int
     uint32_t nflags = 0;
     int64_t total = 0;
     for (int oi = 0; oi < IGG_NOFFSETS; ++oi) {
+        plan.region_pack[oi] = total; plan.region_need[oi] = 0;
+        plan.flag_pack[oi] = nflags;  plan.flag_need[oi] = 0;
+    }
+    for (int oi = 0; oi < IGG_NOFFSETS; ++oi) {
         int o[3];
         index_offset(oi, o);
+        plan.region_pack[oi] = total;
+        plan.flag_pack[oi] = nflags;
+        // (the needs of offset oi are filled in after its fields, below)
+        struct Close { Plan& p; int oi; int64_t& total; uint32_t& nflags;
+                       ~Close() { p.region_need[oi] = total - p.region_pack[oi]; p.flag_need[oi] = nflags - p.flag_pack[oi]; } } close{plan, oi, total, nflags};
         if (!o[0] && !o[1] && !o[2]) continue;
         plan.peer[oi] = -1;
         for (int i = 0; i < nfields; ++i) {
@@ -602,7 +611,8 @@ int igg_plan_describe(const igg_grid_desc* desc, int nfields, const igg_field* f
 }
 
 int igg_plan_tiles(const igg_grid_desc* desc, int nfields, const igg_field* fields, const int* dims_order, int ndims_order,
-                   int mode, void* tiles_out, int tiles_cap, int* ntiles_out, int64_t* staging_bytes_out) {
+                   int mode, void* tiles_out, int tiles_cap, int* ntiles_out, int64_t* staging_bytes_out,
+                   int64_t* regions_out) {
     if (!desc || !fields || !ntiles_out) return igg::fail(IGG_ERR_ARG, "igg_plan_tiles: NULL argument.");
     if (mode != IGG_MODE_IPC_1PHASE && mode != IGG_MODE_IPC_LL128) return igg::fail(IGG_ERR_ARG, "igg_plan_tiles: mode must be an IPC mode.");
     int mask;
@@ -613,6 +623,13 @@ int igg_plan_tiles(const igg_grid_desc* desc, int nfields, const igg_field* fiel
     if (rc) return rc;
     *ntiles_out = (int)plan.tiles.size();
     if (staging_bytes_out) *staging_bytes_out = plan.staging_bytes;
+    if (regions_out)
+        for (int o = 0; o < IGG_NOFFSETS; ++o) {
+            regions_out[o] = plan.region_pack[o];
+            regions_out[IGG_NOFFSETS + o] = plan.region_need[o];
+            regions_out[2 * IGG_NOFFSETS + o] = plan.flag_pack[o];
+            regions_out[3 * IGG_NOFFSETS + o] = plan.flag_need[o];
+        }
     if (tiles_out) {
         if (tiles_cap < (int)plan.tiles.size()) return igg::fail(IGG_ERR_ARG, "igg_plan_tiles: tiles_cap too small (need %d).", (int)plan.tiles.size());
         std::memcpy(tiles_out, plan.tiles.data(), plan.tiles.size() * sizeof(igg::TileRec));

@@ -16,6 +16,7 @@ IGG_ERR_ARG, IGG_ERR_CUDA, IGG_ERR_STATE, IGG_ERR_FIELDS, IGG_ERR_IPC = -1, -2, 
 IGG_ERR_NCCL, IGG_ERR_TIMEOUT, IGG_ERR_UNSUPPORTED, IGG_ERR_GRID = -6, -7, -8, -9
 IGG_SYNC, IGG_ASYNC = 0, 1
 IGG_MODE_IPC_1PHASE, IGG_MODE_NCCL_3PHASE, IGG_MODE_IPC_LL128 = 0, 1, 2
+IGG_NOFFSETS = 27
 IGG_OP_PUSH, IGG_OP_LOCAL, IGG_OP_UNPACK = 0, 1, 2
 IGG_PROC_NULL = -1
 IGG_MAX_FIELDS = 32
@@ -90,7 +91,7 @@ def load():
         "igg_recvranges": (C.c_int, [gd, fp, i32, i32, i64p]),
         "igg_check_fields": (C.c_int, [gd, i32, fp]),
         "igg_plan_describe": (C.c_int, [gd, i32, fp, i32p, i32, C.POINTER(PlanOp), i32, i32p, i64p]),
-        "igg_plan_tiles": (C.c_int, [gd, i32, fp, i32p, i32, i32, vp, i32, i32p, i64p]),
+        "igg_plan_tiles": (C.c_int, [gd, i32, fp, i32p, i32, i32, vp, i32, i32p, i64p, i64p]),
         "igg_ctrl_selftest_create": (C.c_int, [i32, i32, C.c_char_p, C.POINTER(vp)]),
         "igg_ctrl_selftest_run": (C.c_int, [vp, i32, i32, C.c_char_p, i32]),
         "igg_debug_state": (C.c_int, [vp, C.POINTER(C.c_uint64)]),
@@ -167,15 +168,22 @@ class TileRec(C.Structure):
                 ("pad2", C.c_uint32)]
 
 
-def plan_tiles(desc: GridDesc, fields, dims=None, mode=IGG_MODE_IPC_1PHASE):
-    """Returns (list[TileRec], staging_bytes): the tile table of the exchange kernel of `mode` (host only)."""
+def plan_tiles(desc: GridDesc, fields, dims=None, mode=IGG_MODE_IPC_1PHASE, regions=False):
+    """Returns (list[TileRec], staging_bytes): the tile table of the exchange kernel of `mode` (host only).
+    With regions=True a third value: dict of four 27-element lists (byte_pack, byte_need, flag_pack, flag_need)."""
     assert C.sizeof(TileRec) == 80
     lib = load()
     arr = (Field * len(fields))(*fields)
     n = C.c_int(0)
     stg = C.c_int64(0)
+    reg = (C.c_int64 * (4 * IGG_NOFFSETS))()
     dptr, nd = (None, 0) if dims is None else ((C.c_int * len(dims))(*dims), len(dims))
-    check(lib.igg_plan_tiles(C.byref(desc), len(fields), arr, dptr, nd, mode, None, 0, C.byref(n), C.byref(stg)))
+    check(lib.igg_plan_tiles(C.byref(desc), len(fields), arr, dptr, nd, mode, None, 0, C.byref(n), C.byref(stg), None))
     tiles = (TileRec * max(1, n.value))()
-    check(lib.igg_plan_tiles(C.byref(desc), len(fields), arr, dptr, nd, mode, tiles, n.value, C.byref(n), C.byref(stg)))
-    return [tiles[i] for i in range(n.value)], stg.value
+    check(lib.igg_plan_tiles(C.byref(desc), len(fields), arr, dptr, nd, mode, tiles, n.value, C.byref(n), C.byref(stg), reg))
+    out = [tiles[i] for i in range(n.value)]
+    if not regions:
+        return out, stg.value
+    r = list(reg)
+    k = IGG_NOFFSETS
+    return out, stg.value, dict(byte_pack=r[:k], byte_need=r[k:2 * k], flag_pack=r[2 * k:3 * k], flag_need=r[3 * k:])

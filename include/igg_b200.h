@@ -207,11 +207,15 @@ int igg_plan_describe(const igg_grid_desc* desc, int nfields, const igg_field* f
                       igg_plan_op* ops_out, int ops_cap, int* nops_out, int64_t* staging_bytes_out);
 /* The tile table the exchange kernel of `mode` (IGG_MODE_IPC_1PHASE or IGG_MODE_IPC_LL128) would walk for this call
  * on this rank: `*ntiles_out` records of 80 bytes each (layout: struct TileRec in csrc/igg_internal.h; PUSH tiles
- * first, then LOCAL, then UNPACK).  Host only, for tests that execute the table without a GPU.  No reference
- * counterpart. */
+ * first, then LOCAL, then UNPACK).  `regions_out` (may be NULL) receives 4 x 27 numbers, indexed by neighbour offset
+ * (ox+1) + 3(oy+1) + 9(oz+1): where that offset's staging slots start in the table's packed layout, how many bytes
+ * of a staging half the offset needs, and the same two for its arrival flags.  (At run time every offset owns a
+ * region whose position does not depend on the call; the launch shifts each offset's base accordingly.)
+ * Host only, for tests that execute the table without a GPU.  No reference counterpart. */
 int igg_plan_tiles(const igg_grid_desc* desc, int nfields, const igg_field* fields,
                    const int* dims_order, int ndims_order, int mode,
-                   void* tiles_out, int tiles_cap, int* ntiles_out, int64_t* staging_bytes_out);
+                   void* tiles_out, int tiles_cap, int* ntiles_out, int64_t* staging_bytes_out,
+                   int64_t* regions_out);
 
 /* Control-plane self test (host only).  After the bootstrap the library talks between ranks through one POSIX
  * shared-memory mailbox per rank (segment re-allocation hand-shakes, the barrier of gather!) -- the places where the

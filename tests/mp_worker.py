@@ -175,6 +175,38 @@ def main():
                     print(f"GATHER MISMATCH case {ci} root {root}", flush=True)
         igg.finalize_global_grid()
         dist.barrier()
+    # Calls with different field sets and `dims=` alternating on ONE context: every neighbour offset keeps its own
+    # staging / flag region across plans (a neighbour that is a call ahead must not write where another neighbour's
+    # data is still being unpacked).  Fresh data before every call, every call checked against the oracle.
+    if not quick:
+        gsz, kw = (13, 9, 10), dict(periodx=1, periody=1, periodz=1)
+        grids = O.make_grids(n, *gsz, **kw)
+        igg.init_global_grid(*gsz, quiet=True, **kw)
+        shp = {"A": (13, 9, 10), "B": (14, 9, 10), "C": (13, 9, 11)}
+        dev = {k: igg.zeros(s, dtype=torch.int64) for k, s in shp.items()}
+        seq = [("A", (1,)), ("AB", (3, 1, 2)), ("B", (2,)), ("A", (3, 1, 2)), ("ABC", (1, 3)), ("C", (3,)),
+               ("BC", (2, 1)), ("A", (1,)), ("ABC", (3, 1, 2)), ("B", (3, 1, 2))] * 2
+        for k, (names, dims) in enumerate(seq):
+            host = {nm: O.random_bits_field(shp[nm], 8, 5000 + 100 * k + 10 * me + i) for i, nm in enumerate(names)}
+            torch.cuda.synchronize()
+            for nm in names:
+                dev[nm].copy_(igg.from_numpy(host[nm]))
+            torch.cuda.synchronize()
+            igg.update_halo(*[dev[nm] for nm in names], dims=dims, blocking=(k % 3 != 1))
+            torch.cuda.synchronize()
+            out = [None] * n
+            dist.all_gather_object(out, [igg.to_numpy(dev[nm]).view(np.uint64) for nm in names])
+            if me == 0:
+                want = [[O.random_bits_field(shp[nm], 8, 5000 + 100 * k + 10 * r + i) for i, nm in enumerate(names)] for r in range(n)]
+                O.update_halo(grids, want, dims=dims)
+                for r in range(n):
+                    for i in range(len(names)):
+                        if not np.array_equal(out[r][i], want[r][i]):
+                            ok = False
+                            print(f"ALTERNATING-PLANS MISMATCH call {k} ({names}, dims {dims}) rank {r} field {i}", flush=True)
+        igg.finalize_global_grid()
+        dist.barrier()
+
     # BASELINE config 2 at full size (256^3 f64, periodic): too big to ship to rank 0, so size-independent checks:
     # (a) the fused path equals the NCCL path (itself checked against the oracle above) bit for bit, on the device;
     # (b) after the update every halo plane equals the neighbour's send plane (checked through torch.distributed).

@@ -136,6 +136,48 @@ def test_tile_tables_match_oracle(case, mode):
             assert np.array_equal(flat_bytes(got[r][i]), flat_bytes(want[r][i])), (r, i)
 
 
+def staged_range(t):
+    """Byte range of a staging half a PUSH / UNPACK tile touches (packed layout of its plan)."""
+    if t.kind in (PUSH_LL, UNPACK_LL):
+        return t.dst_off + t.row0 * LINE, t.dst_off + (t.row0 + t.nrows) * LINE
+    off, sy, sz = (t.dst_off, t.dst_sy, t.dst_sz) if t.kind == PUSH else (t.src_off, t.src_sy, t.src_sz)
+    lo, hi = None, None
+    for row in (t.row0, t.row0 + t.nrows - 1):
+        y, z = row % t.ny, row // t.ny
+        a = off + y * sy + z * sz
+        lo = a if lo is None else min(lo, a)
+        hi = max(hi or 0, a + (t.ncols << t.vec_log2))
+    return lo, hi
+
+
+@pytest.mark.parametrize("mode", [L.IGG_MODE_IPC_1PHASE, L.IGG_MODE_IPC_LL128], ids=["fence", "ll128"])
+@pytest.mark.parametrize("case", CASES, ids=[f"c{i}" for i in range(len(CASES))])
+def test_every_tile_stays_inside_its_offsets_region(case, mode):
+    """At run time every neighbour offset owns a region of the staging half (and of the flag array) whose position
+    does not depend on the plan; the launch shifts an offset's base by (region - packed start).  That is only sound
+    if everything a tile touches lies inside the packed range of ITS offset: the receiver's offset (26 - nbr) for
+    PUSH, its own (nbr) for UNPACK."""
+    nprocs, gsz, kw, shapes, hws, elsize, dims = case
+    grids = O.make_grids(nprocs, *gsz, **kw)
+    hws = hws or [grids[0].halowidths] * len(shapes)
+    for g in grids:
+        cf = [L.make_field(0x10000 * (i + 1), s, hws[i], elsize) for i, s in enumerate(shapes)]
+        tiles, stg, reg = L.plan_tiles(desc_of(g), cf, dims, mode, regions=True)
+        assert sum(reg["byte_need"]) == stg and all(n % 128 == 0 for n in reg["byte_need"])
+        for o in range(27):
+            assert reg["byte_pack"][o] == sum(reg["byte_need"][:o]) and reg["flag_pack"][o] == sum(reg["flag_need"][:o])
+        for t in tiles:
+            if t.kind == LOCAL:
+                continue
+            o = 26 - t.nbr if t.kind in (PUSH, PUSH_LL) else t.nbr
+            lo, hi = staged_range(t)
+            assert reg["byte_pack"][o] <= lo and hi <= reg["byte_pack"][o] + reg["byte_need"][o], (t.kind, t.nbr)
+            if t.kind in (PUSH, UNPACK):
+                assert reg["flag_pack"][o] <= t.flag_idx < reg["flag_pack"][o] + reg["flag_need"][o]
+            else:
+                assert sum(reg["flag_need"]) == 0
+
+
 @pytest.mark.parametrize("mode", [L.IGG_MODE_IPC_1PHASE, L.IGG_MODE_IPC_LL128], ids=["fence", "ll128"])
 @pytest.mark.parametrize("ci,case", [(i, c) for i, c in G.cases() if c["nprocs"] > 1], ids=[c["name"] for _, c in G.cases() if c["nprocs"] > 1])
 def test_tile_tables_match_golden(ci, case, mode):
