@@ -282,6 +282,16 @@ int build_plan(const igg_grid_desc& g, int nfields, const igg_field* fields, int
             halo[i][d] = ((dims_mask >> d) & 1) && field_ol(g, fields[i], d) >= 2 * fields[i].halowidths[d] &&
                          (g.dims[d] > 1 || g.periods[d]);   // no rank has a neighbour in d otherwise (global fact)
 
+    // Every rank must take part in a call or none (the exchange epoch is compared across ranks).  An array without
+    // interior cells in an exchanged dimension could leave interior ranks with nothing to copy: refuse it loudly.
+    for (int i = 0; i < nfields; ++i)
+        for (int d = 0; d < 3; ++d)
+            if (halo[i][d] && g.nprocs > 1 && fields[i].size[d] <= 2 * fields[i].halowidths[d])
+                return fail(IGG_ERR_UNSUPPORTED,
+                            "The field at position %d has no interior cells in dimension %d (size %lld <= 2*halowidth %lld); "
+                            "such arrays are not supported on more than one rank.", i + 1, d + 1,
+                            (long long)fields[i].size[d], (long long)(2 * fields[i].halowidths[d]));
+
     // Staging slots: one per (offset, field), identical on every rank (depends only on field sizes, halowidths and
     // the updated dimensions, never on which neighbours exist), so a sender can compute the receiver's layout.
     std::vector<int64_t> slot_off((size_t)IGG_NOFFSETS * nfields, -1);

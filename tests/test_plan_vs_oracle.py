@@ -200,6 +200,13 @@ def test_error_paths():
     bad.neighbors[0][1] = L.IGG_PROC_NULL          # left = me, right = PROC_NULL
     with pytest.raises(L.IGGError, match="Incoherent neighbors in dimension 1"):
         L.plan_describe(bad, [fa])
+    # several ranks: an array made of halo cells only in an exchanged dimension is refused (interior ranks would
+    # have nothing to copy, and every rank must take part in a call or none)
+    two = L.make_desc((4, 8, 8), (2, 1, 1), (0, 0, 0), ((-1, -1, -1), (1, -1, -1)), (0, 0, 0), (4, 2, 2), (2, 1, 1), 0, 2, 0)
+    thin = L.make_field(0x1000, (4, 8, 8), (2, 1, 1), 8)
+    with pytest.raises(L.IGGError, match="has no interior cells in dimension 1"):
+        L.plan_describe(two, [thin])
+    L.plan_describe(two, [L.make_field(0x1000, (5, 8, 8), (2, 1, 1), 8)])      # one interior plane: fine
 
 
 def test_c_ranges_match_reference_known_answers():
