@@ -5,6 +5,7 @@
 // (arrival flags + counters), the double-buffered receive staging, cached plans and peer mappings; user arrays are
 // only borrowed for the duration of a call.
 #include <cuda_runtime.h>
+#include <time.h>
 #include <unistd.h>
 
 #include <cstdlib>
@@ -74,33 +75,45 @@ static uint64_t process_nonce() {
 
 using namespace igg;
 
+struct igg_prepared;
+
 struct igg_ctx {
     igg_grid_desc g;
     int device = 0;
-    int mode = IGG_MODE_IPC_LL128;              // default protocol (IGG_MODE=fence selects IGG_MODE_IPC_1PHASE)
-    char* ctrl = nullptr;                       // device: flags at 0, counters at kCountersOff
+    int mode = IGG_MODE_IPC_AUTO;               // default: protocol chosen per call by size (IGG_MODE=fence|ll128 forces one)
+    char* ctrl = nullptr;                       // device: exchange state at 0, arrival flags at kFlagsOff
     char* staging = nullptr;                    // device: two halves
     int64_t staging_half = 0;
     int* h_status = nullptr;                    // host-mapped status word
     int* d_status = nullptr;
+    unsigned long long* h_done = nullptr;       // host-mapped completion word of host-synchronous calls
+    unsigned long long* d_done = nullptr;
+    unsigned long long ticket = 0;              // value the next host-synchronous launch stores into *h_done
+    bool spin_wait = true;                      // IGG_BLOCKING=sync: wait with cudaStreamSynchronize instead
     ControlPlane cp;
     std::string shm_name;
     std::vector<Peer> peers;
     bool bootstrapped = false;
     std::vector<std::unique_ptr<Plan>> plans;
+    std::vector<igg_prepared*> prepared;        // live prepared calls (they hold Plan pointers of this context)
     int max_blocks = 0;
     int64_t launches = 0;
     cudaStream_t last_stream = nullptr;
     cudaEvent_t last_event = nullptr;
     bool have_last = false;
-    // Staging / flag REGIONS, one per neighbour offset, identical on every rank (they only depend on the sequence of
-    // plans seen, and update_halo is collective): bytes inside one staging half and arrival-flag words.  Grow-only.
-    int64_t  region_cap[IGG_NOFFSETS] = {0}, region_off[IGG_NOFFSETS] = {0};
+    // Staging / flag REGIONS, one per neighbour offset and protocol ([0] fence, [1] LL128), identical on every rank
+    // (they only depend on the sequence of plans seen, and update_halo is collective): bytes inside one staging half
+    // and arrival-flag words.  Grow-only.  A half is [LL128 regions | fence regions]: LL128 lines are only ever
+    // polled where LL128 lines are written, so payload of the other protocol cannot be mistaken for an epoch word.
+    int64_t  region_cap[2][IGG_NOFFSETS] = {{0}}, region_off[2][IGG_NOFFSETS] = {{0}};
     uint32_t flag_cap[IGG_NOFFSETS] = {0}, flag_off[IGG_NOFFSETS] = {0};
     cudaStream_t side_stream = nullptr;         // host-resident fields: the wrap-lines kernel runs beside the exchange
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     unsigned long long timeout_ns = 20ull * 1000000000ull;
-    struct PtrEntry { const void* user = nullptr; void* resolved = nullptr; bool host = false; };
+    // Pointer classification cache.  Only entries whose device alias equals the user pointer are kept, so a stale
+    // entry (memory freed and the address handed out again as another kind of memory) can at worst pick the other of
+    // two equivalent kernels for an x self-wrap, never a wrong address.
+    struct PtrEntry { const void* user = nullptr; bool host = false; };
     PtrEntry ptr_cache[64];
     // gather
     char* gather_buf = nullptr;   int64_t gather_bytes = 0;       // root: device image of A_global (peer mapped)
@@ -111,6 +124,20 @@ struct igg_ctx {
     // optional kernel timeline (igg_trace_enable)
     unsigned long long* d_trace = nullptr;
     int last_grid = 0;
+};
+
+// A validated update_halo call kept for reuse (igg_prepare): resolved field pointers and the plan.
+struct igg_prepared {
+    igg_ctx* ctx = nullptr;
+    int nfields = 0;
+    igg_field fields[IGG_MAX_FIELDS];           // pointers resolved to device addresses
+    igg_field user_fields[IGG_MAX_FIELDS];      // as passed in (for the NCCL comparison path)
+    uint8_t host_lines[IGG_MAX_FIELDS];
+    int dims_mask = 7;
+    int dims_order[3] = {3, 1, 2};
+    int ndims_order = 3;
+    int mode = -1;                              // ctx->mode the plan was chosen under
+    Plan* plan = nullptr;
 };
 
 // ---- helpers -----------------------------------------------------------------------------------------------------
@@ -192,41 +219,97 @@ static int grow_staging(igg_ctx* ctx, int64_t need_half) {
     return IGG_OK;
 }
 
+// The per-plan launch constants for the context's current staging layout.
+static void fill_plan_dev(const igg_ctx* ctx, const Plan& plan, PlanDev& d) {
+    std::memset(&d, 0, sizeof(d));
+    const int pr = plan.ll128 ? 1 : 0;
+    d.active_mask = plan.active_mask;
+    d.unpack_half = ctx->staging_half;
+    for (int oi = 0; oi < IGG_NOFFSETS; ++oi) {
+        if (!((plan.active_mask >> oi) & 1u)) continue;
+        const Peer& peer = ctx->peers[plan.peer[oi]];
+        // The tiles carry offsets / flag numbers of the plan's own packed layout; shift every offset's base to that
+        // offset's region (same table on every rank).  What I push at offset oi lands in the receiver's region of
+        // the opposite offset.
+        const int ro = opposite_index(oi);
+        d.push_base[oi] = peer.staging.ptr + (ctx->region_off[pr][ro] - plan.region_pack[ro]);
+        d.push_half[oi] = peer.staging.bytes;
+        d.unpack_base[oi] = ctx->staging + (ctx->region_off[pr][oi] - plan.region_pack[oi]);
+        d.remote_flags[oi] = reinterpret_cast<unsigned long long*>(peer.ctrl.ptr + kFlagsOff) +
+                             ((long long)ctx->flag_off[ro] - (long long)plan.flag_pack[ro]);
+        d.local_flag_delta[oi] = (int32_t)((long long)ctx->flag_off[oi] - (long long)plan.flag_pack[oi]);
+    }
+}
+
+// Host -> device copy of a small table that is complete when the call returns (a pageable-memory cudaMemcpy may
+// return while its DMA is still in flight, and the caller's stream need not be ordered against the legacy stream).
+static cudaError_t upload_now(void* dst, const void* src, size_t bytes) {
+    cudaError_t e = cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, cudaStreamLegacy);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(cudaStreamLegacy);
+    return e;
+}
+
+static int upload_plan_dev(igg_ctx* ctx, Plan& plan) {
+    if (!plan.d_plan) return IGG_OK;
+    PlanDev d;
+    fill_plan_dev(ctx, plan, d);
+    const cudaError_t e = upload_now(plan.d_plan, &d, sizeof(d));
+    if (e != cudaSuccess) return fail(IGG_ERR_CUDA, "plan constants upload failed: %s", cudaGetErrorString(e));
+    return IGG_OK;
+}
+
 // Makes sure every neighbour offset's region (staging bytes, arrival flags) is large enough for `plan`.  Regions keep
 // their place from call to call, so data a neighbour pushes for one offset can never land on memory another
 // offset's neighbour writes or this rank still reads -- also when calls with different field sets or `dims=`
 // alternate and the ranks are not in lock-step.  Growing is collective and rare (first use of a bigger plan): every
-// rank reaches the same decision at the same call because the needs depend on the call's arguments only.
+// rank reaches the same decision at the same call because the needs depend on the call's arguments only.  It blocks
+// the host (device synchronisation + barrier across ranks), also for IGG_ASYNC calls.
 static int ensure_layout(igg_ctx* ctx, const Plan& plan) {
+    const int pr = plan.ll128 ? 1 : 0;
     bool grow = false;
     for (int o = 0; o < IGG_NOFFSETS; ++o)
-        grow = grow || plan.region_need[o] > ctx->region_cap[o] || plan.flag_need[o] > ctx->flag_cap[o];
+        grow = grow || plan.region_need[o] > ctx->region_cap[pr][o] || plan.flag_need[o] > ctx->flag_cap[o];
     if (!grow) return IGG_OK;
-    int64_t cap[IGG_NOFFSETS], total = 0;
+    int64_t cap[2][IGG_NOFFSETS], total = 0;
     uint64_t fcap[IGG_NOFFSETS], ftotal = 0;
+    for (int q = 0; q < 2; ++q)
+        for (int o = 0; o < IGG_NOFFSETS; ++o) {
+            cap[q][o] = ctx->region_cap[q][o];
+            if (q == pr && plan.region_need[o] > cap[q][o])
+                cap[q][o] = (plan.region_need[o] + plan.region_need[o] / 4 + 127) / 128 * 128;
+            total += cap[q][o];
+        }
     for (int o = 0; o < IGG_NOFFSETS; ++o) {
-        cap[o] = ctx->region_cap[o];
-        if (plan.region_need[o] > cap[o]) cap[o] = (plan.region_need[o] + plan.region_need[o] / 4 + 127) / 128 * 128;
         fcap[o] = ctx->flag_cap[o];
         if (plan.flag_need[o] > fcap[o]) fcap[o] = plan.flag_need[o];
-        total += cap[o];
         ftotal += fcap[o];
     }
     if (ftotal > (uint64_t)kMaxFlags)
         return fail(IGG_ERR_ARG, "update_halo: the calls made so far need %llu arrival flags, the control segment holds %d; "
-                    "use the LL128 protocol (default) or split the call.", (unsigned long long)ftotal, kMaxFlags);
+                    "use the LL128 protocol or split the call.", (unsigned long long)ftotal, kMaxFlags);
     int rc;
     if (total > ctx->staging_half) {
-        rc = grow_staging(ctx, total);              // quiesces all ranks, re-allocates, re-maps
+        rc = grow_staging(ctx, total);              // quiesces all ranks, re-allocates (zeroed), re-maps
+        if (rc) return rc;
     } else {
         CU(cudaDeviceSynchronize());                // nobody exchanges while the regions move
         rc = ctx->cp.barrier();
+        if (rc) return rc;
+        // An LL128 region may now lie where another protocol's payload was: no stale word may look like an epoch.
+        CU(cudaMemset(ctx->staging, 0, (size_t)(2 * ctx->staging_half)));
+        CU(cudaDeviceSynchronize());
+        rc = ctx->cp.barrier();
+        if (rc) return rc;
     }
-    if (rc) return rc;
     total = 0; ftotal = 0;
-    for (int o = 0; o < IGG_NOFFSETS; ++o) {
-        ctx->region_cap[o] = cap[o];  ctx->region_off[o] = total;          total += cap[o];
-        ctx->flag_cap[o] = (uint32_t)fcap[o]; ctx->flag_off[o] = (uint32_t)ftotal; ftotal += fcap[o];
+    for (int q = 1; q >= 0; --q)                    // [LL128 regions | fence regions]
+        for (int o = 0; o < IGG_NOFFSETS; ++o) { ctx->region_cap[q][o] = cap[q][o]; ctx->region_off[q][o] = total; total += cap[q][o]; }
+    for (int o = 0; o < IGG_NOFFSETS; ++o) { ctx->flag_cap[o] = (uint32_t)fcap[o]; ctx->flag_off[o] = (uint32_t)ftotal; ftotal += fcap[o]; }
+    // Every cached plan's launch constants follow the new layout (launches captured into CUDA graphs stay valid:
+    // they hold the pointer to the constants, not the constants).
+    for (auto& up : ctx->plans) {
+        rc = upload_plan_dev(ctx, *up);
+        if (rc) return rc;
     }
     return IGG_OK;
 }
@@ -235,32 +318,36 @@ static int ensure_layout(igg_ctx* ctx, const Plan& plan) {
 // through its device alias.  Pageable host memory is rejected (no CPU fallback, no hidden copies in update_halo).
 static int resolve_pointer(igg_ctx* ctx, const void* p, void** out, bool* is_host) {
     igg_ctx::PtrEntry& ce = ctx->ptr_cache[((uintptr_t)p >> 8) & 63];
-    if (ce.user == p) { *out = ce.resolved; if (is_host) *is_host = ce.host; return IGG_OK; }
+    if (ce.user == p) { *out = const_cast<void*>(p); if (is_host) *is_host = ce.host; return IGG_OK; }
     cudaPointerAttributes a;
     cudaError_t e = cudaPointerGetAttributes(&a, p);
     if (e != cudaSuccess) { cudaGetLastError(); return fail(IGG_ERR_CUDA, "cudaPointerGetAttributes failed: %s", cudaGetErrorString(e)); }
     if (a.type == cudaMemoryTypeDevice || a.type == cudaMemoryTypeManaged) {
         *out = const_cast<void*>(p);
         if (is_host) *is_host = false;
-        ce.user = p; ce.resolved = *out; ce.host = false;
+        ce.user = p; ce.host = false;
         return IGG_OK;
     }
     if (a.type == cudaMemoryTypeHost && a.devicePointer) {
         *out = a.devicePointer;
         if (is_host) *is_host = true;
-        ce.user = p; ce.resolved = *out; ce.host = true;
+        if (a.devicePointer == p) { ce.user = p; ce.host = true; }
         return IGG_OK;
     }
     return fail(IGG_ERR_UNSUPPORTED,
                 "pointer %p is pageable host memory: pass device memory or page-locked (pinned/registered) host memory.", p);
 }
 
+static int proto_of_mode(int mode) {
+    return mode == IGG_MODE_IPC_LL128 ? kProtoLL128 : mode == IGG_MODE_IPC_AUTO ? kProtoAuto : kProtoFence;
+}
+
 static Plan* find_or_build_plan(igg_ctx* ctx, int nfields, const igg_field* fields, int dims_mask, const uint8_t* host_lines,
                                 int* rc_out) {
-    const bool ll128 = ctx->mode == IGG_MODE_IPC_LL128;
+    const int proto = proto_of_mode(ctx->mode);
     for (auto& up : ctx->plans) {
         Plan* p = up.get();
-        if (p->dims_mask != dims_mask || (int)p->key.size() != nfields || p->ll128 != ll128) continue;
+        if (p->dims_mask != dims_mask || (int)p->key.size() != nfields || p->proto_req != proto) continue;
         bool same = true;
         for (int i = 0; i < nfields && same; ++i) {
             const FieldKey& k = p->key[i];
@@ -272,28 +359,37 @@ static Plan* find_or_build_plan(igg_ctx* ctx, int nfields, const igg_field* fiel
         if (same) { *rc_out = IGG_OK; return p; }
     }
     std::unique_ptr<Plan> plan(new Plan());
-    int rc = build_plan(ctx->g, nfields, fields, dims_mask, *plan, host_lines, ll128);
+    int rc = build_plan(ctx->g, nfields, fields, dims_mask, *plan, host_lines, proto);
     if (rc) { *rc_out = rc; return nullptr; }
-    if (!plan->tiles.empty()) {
-        cudaError_t e = cudaMalloc(&plan->d_tiles, plan->tiles.size() * sizeof(TileRec));
-        if (e == cudaSuccess)
-            e = cudaMemcpy(plan->d_tiles, plan->tiles.data(), plan->tiles.size() * sizeof(TileRec), cudaMemcpyHostToDevice);
-        if (e != cudaSuccess) { *rc_out = fail(IGG_ERR_CUDA, "plan upload failed: %s", cudaGetErrorString(e)); return nullptr; }
-        plan->grid = (int)std::min<int64_t>((int64_t)plan->tiles.size(), ctx->max_blocks);
+    plan->proto_req = proto;
+    {
+        // One allocation: [PlanDev | tile table].
+        const size_t head = (sizeof(PlanDev) + 255) & ~size_t(255);
+        char* mem = nullptr;
+        cudaError_t e = cudaMalloc(&mem, head + std::max<size_t>(plan->tiles.size(), 1) * sizeof(TileRec));
+        if (e == cudaSuccess && !plan->tiles.empty())
+            e = upload_now(mem + head, plan->tiles.data(), plan->tiles.size() * sizeof(TileRec));
+        if (e != cudaSuccess) { if (mem) cudaFree(mem); *rc_out = fail(IGG_ERR_CUDA, "plan upload failed: %s", cudaGetErrorString(e)); return nullptr; }
+        plan->d_plan = reinterpret_cast<PlanDev*>(mem);
+        plan->d_tiles = reinterpret_cast<TileRec*>(mem + head);
+        plan->grid = (int)std::max<int64_t>(1, std::min<int64_t>((int64_t)plan->tiles.size(), ctx->max_blocks));
     }
     if (!plan->wrap_tiles.empty()) {
         cudaError_t e = cudaMalloc(&plan->d_wrap_tiles, plan->wrap_tiles.size() * sizeof(TileRec));
-        if (e == cudaSuccess)
-            e = cudaMemcpy(plan->d_wrap_tiles, plan->wrap_tiles.data(), plan->wrap_tiles.size() * sizeof(TileRec), cudaMemcpyHostToDevice);
-        if (e != cudaSuccess) { *rc_out = fail(IGG_ERR_CUDA, "plan upload failed: %s", cudaGetErrorString(e)); return nullptr; }
+        if (e == cudaSuccess) e = upload_now(plan->d_wrap_tiles, plan->wrap_tiles.data(), plan->wrap_tiles.size() * sizeof(TileRec));
+        if (e != cudaSuccess) { cudaFree(plan->d_plan); *rc_out = fail(IGG_ERR_CUDA, "plan upload failed: %s", cudaGetErrorString(e)); return nullptr; }
     }
-    if (ctx->plans.size() >= 64) {   // bound the cache (fields of ever-changing shapes)
-        if (ctx->plans.front()->d_tiles || ctx->plans.front()->d_wrap_tiles) {
+    // Bound the cache (fields of ever-changing shapes): drop the oldest plan that nothing can still refer to.  Plans
+    // behind a prepared call, or launched while their stream was being captured into a CUDA graph, are never dropped.
+    if (ctx->plans.size() >= 256) {
+        for (size_t k = 0; k < ctx->plans.size(); ++k) {
+            if (ctx->plans[k]->pinned) continue;
             cudaDeviceSynchronize();
-            cudaFree(ctx->plans.front()->d_tiles);
-            cudaFree(ctx->plans.front()->d_wrap_tiles);
+            cudaFree(ctx->plans[k]->d_plan);
+            cudaFree(ctx->plans[k]->d_wrap_tiles);
+            ctx->plans.erase(ctx->plans.begin() + (long)k);
+            break;
         }
-        ctx->plans.erase(ctx->plans.begin());
     }
     ctx->plans.push_back(std::move(plan));
     *rc_out = IGG_OK;
@@ -315,14 +411,41 @@ static void remember_launch(igg_ctx* ctx, cudaStream_t stream) {
     ctx->launches += 1;
 }
 
+// A device-side time-out of an earlier launch (also of a stream-ordered one nobody waited for) is reported by the
+// next call of any kind.
 static int check_status(igg_ctx* ctx) {
-    if (*ctx->h_status != 0) {
+    if (*reinterpret_cast<volatile int*>(ctx->h_status) != 0) {
         const int s = *ctx->h_status;
         *ctx->h_status = 0;
         return fail(s, "update_halo: a neighbour rank did not deliver its halo within %.1f s (device-side time-out).",
                     ctx->timeout_ns * 1e-9);
     }
     return IGG_OK;
+}
+
+static int make_current(igg_ctx* ctx) {
+    int cur = -1;
+    if (cudaGetDevice(&cur) == cudaSuccess && cur == ctx->device) return IGG_OK;
+    CU(cudaSetDevice(ctx->device));
+    return IGG_OK;
+}
+
+// Host-synchronous completion.  `ticket` != 0: the launch stores it into the mapped word *h_done when its last block
+// has finished, and the host polls that word (a stream synchronisation costs several microseconds more); the stream
+// is queried now and then so that a failed launch or a fault cannot hang the caller.
+static int wait_done(igg_ctx* ctx, cudaStream_t stream, unsigned long long ticket) {
+    if (ticket) {
+        for (unsigned spins = 1;; ++spins) {
+            if (__atomic_load_n(ctx->h_done, __ATOMIC_ACQUIRE) == ticket) return check_status(ctx);
+            if ((spins & 0xfffu) == 0) {
+                const cudaError_t q = cudaStreamQuery(stream);
+                if (q == cudaSuccess) return check_status(ctx);
+                if (q != cudaErrorNotReady) return fail(IGG_ERR_CUDA, "update_halo: %s", cudaGetErrorString(q));
+            }
+        }
+    }
+    CU(cudaStreamSynchronize(stream));
+    return check_status(ctx);
 }
 
 // ---- C ABI -------------------------------------------------------------------------------------------------------
@@ -341,23 +464,30 @@ int igg_create(const igg_grid_desc* desc, igg_ctx** out) {
     // ref: src/select_device.jl:30
     if (desc->device < 0 || desc->device >= ndev)
         return fail(IGG_ERR_ARG, "More processes have been launched per node than there are GPUs available.");
-    std::unique_ptr<igg_ctx> ctx(new igg_ctx());
+    // Whatever fails below, igg_destroy releases what has been set up so far (it copes with a half-built context).
+    struct Guard { igg_ctx* c; ~Guard() { if (c) { const std::string keep = last_error_cstr(); igg_destroy(c); set_error("%s", keep.c_str()); } } } guard{new igg_ctx()};
+    igg_ctx* ctx = guard.c;
     ctx->g = *desc;
     ctx->device = desc->device;
     CU(cudaSetDevice(ctx->device));
     CU(cudaMalloc(&ctx->ctrl, kCtrlBytes));
     CU(cudaMemset(ctx->ctrl, 0, kCtrlBytes));
-    CU(cudaHostAlloc(&ctx->h_status, sizeof(int), cudaHostAllocMapped));
+    CU(cudaHostAlloc(&ctx->h_status, 64, cudaHostAllocMapped));
     *ctx->h_status = 0;
     CU(cudaHostGetDevicePointer(&ctx->d_status, ctx->h_status, 0));
+    ctx->h_done = reinterpret_cast<unsigned long long*>(ctx->h_status) + 4;      // same page-locked block, own 32 bytes
+    ctx->d_done = reinterpret_cast<unsigned long long*>(ctx->d_status) + 4;
+    *ctx->h_done = 0;
     CU(cudaEventCreateWithFlags(&ctx->last_event, cudaEventDisableTiming));
     ctx->max_blocks = halo_kernel_max_coresident_blocks(ctx->device);
     if (ctx->max_blocks <= 0) return fail(IGG_ERR_CUDA, "occupancy query for the halo kernel failed (was the library built for sm_100a?): %s", cudaGetErrorString(cudaGetLastError()));
     if (const char* t = getenv("IGG_DEVICE_TIMEOUT_S")) ctx->timeout_ns = (unsigned long long)(atof(t) * 1e9);
-    // IGG_MODE=fence / ll128: the IPC protocol a new context starts in (default ll128; the same on every rank).
+    if (const char* b = getenv("IGG_BLOCKING")) ctx->spin_wait = strcmp(b, "sync") != 0;
+    // IGG_MODE=fence / ll128 / auto: the IPC protocol a new context starts in (default auto; the same on every rank).
     if (const char* m = getenv("IGG_MODE")) {
         if (!strcmp(m, "ll128")) ctx->mode = IGG_MODE_IPC_LL128;
         else if (!strcmp(m, "fence") || !strcmp(m, "ipc")) ctx->mode = IGG_MODE_IPC_1PHASE;
+        else if (!strcmp(m, "auto")) ctx->mode = IGG_MODE_IPC_AUTO;
     }
     ctx->peers.resize(desc->nprocs);
     if (desc->nprocs > 1) {
@@ -367,7 +497,8 @@ int igg_create(const igg_grid_desc* desc, igg_ctx** out) {
         ctx->bootstrapped = true;
     }
     CU(cudaDeviceSynchronize());
-    *out = ctx.release();
+    *out = ctx;
+    guard.c = nullptr;
     return IGG_OK;
 }
 
@@ -376,10 +507,11 @@ int igg_destroy(igg_ctx* ctx) {
     cudaSetDevice(ctx->device);
     cudaDeviceSynchronize();
     if (ctx->g.nprocs > 1 && ctx->cp.attached()) ctx->cp.barrier();   // nobody is still writing into my segments
+    for (igg_prepared* h : ctx->prepared) { h->ctx = nullptr; h->plan = nullptr; }   // handles outlive the context harmlessly
     nccl_free(ctx->nccl);
     ctx->nccl = nullptr;
     for (auto& p : ctx->peers) { close_segment(p.ctrl); close_segment(p.staging); close_segment(p.gather); }
-    for (auto& pl : ctx->plans) { cudaFree(pl->d_tiles); cudaFree(pl->d_wrap_tiles); }
+    for (auto& pl : ctx->plans) { cudaFree(pl->d_plan); cudaFree(pl->d_wrap_tiles); }
     if (ctx->staging) cudaFree(ctx->staging);
     if (ctx->gather_buf) cudaFree(ctx->gather_buf);
     if (ctx->gather_src) cudaFree(ctx->gather_src);
@@ -440,33 +572,22 @@ int igg_bootstrap_import(igg_ctx* ctx, const void* all_blobs, int nprocs) {
 
 int igg_set_mode(igg_ctx* ctx, int mode) {
     if (!ctx) return fail(IGG_ERR_ARG, "igg_set_mode: NULL context.");
-    if (mode != IGG_MODE_IPC_1PHASE && mode != IGG_MODE_NCCL_3PHASE && mode != IGG_MODE_IPC_LL128)
+    if (mode != IGG_MODE_IPC_1PHASE && mode != IGG_MODE_NCCL_3PHASE && mode != IGG_MODE_IPC_LL128 && mode != IGG_MODE_IPC_AUTO)
         return fail(IGG_ERR_ARG, "igg_set_mode: unknown mode %d.", mode);
     if (mode == IGG_MODE_NCCL_3PHASE && ctx->g.nprocs > 1 && !ctx->nccl)
         return fail(IGG_ERR_STATE, "igg_set_mode: call igg_nccl_init before selecting IGG_MODE_NCCL_3PHASE.");
-    const bool was_ll = ctx->mode == IGG_MODE_IPC_LL128, is_ll = mode == IGG_MODE_IPC_LL128;
-    if (was_ll != is_ll && ctx->g.nprocs > 1 && ctx->bootstrapped) {
-        // Entering or leaving the line format is collective: the other protocol's payload may sit where LL128 expects
-        // a line's epoch word, so the staging memory of every rank is cleared while nobody exchanges.
-        CU(cudaSetDevice(ctx->device));
-        CU(cudaDeviceSynchronize());
-        int rc = ctx->cp.barrier();
-        if (rc) return rc;
-        if (ctx->staging) CU(cudaMemset(ctx->staging, 0, (size_t)(2 * ctx->staging_half)));
-        CU(cudaDeviceSynchronize());
-        rc = ctx->cp.barrier();
-        if (rc) return rc;
-    }
+    // The two IPC protocols stage in regions of their own (ensure_layout), so switching needs no clean-up.
     ctx->mode = mode;
     return IGG_OK;
 }
 
-// The fused single-phase exchange for the dimensions in `dims_mask` (plan lookup, staging growth, one launch).
-static int launch_exchange(igg_ctx* ctx, int nfields, const igg_field* fields, int dims_mask, cudaStream_t stream,
-                           const uint8_t* host_lines = nullptr) {
+}  // extern "C"
+
+// Launches `plan` for `fields` (pointers already resolved).  `sync`: the call is host-synchronous.
+static int launch_plan(igg_ctx* ctx, Plan* plan, int nfields, const igg_field* fields, cudaStream_t stream, bool sync,
+                       bool* waited) {
     int rc;
-    Plan* plan = find_or_build_plan(ctx, nfields, fields, dims_mask, host_lines, &rc);
-    if (!plan) return rc;
+    *waited = false;
     bool join_side = false;
     if (!plan->wrap_tiles.empty()) {
         // Whole-line x self-wrap of host-resident fields: its own kernel, independent of the other tiles of the call.
@@ -494,7 +615,9 @@ static int launch_exchange(igg_ctx* ctx, int nfields, const igg_field* fields, i
         if (join_side) CU(cudaEventRecord(ctx->ev_join, ws));
         remember_launch(ctx, stream);
     }
-    if (plan->tiles.empty()) return IGG_OK;                       // e.g. one rank, nothing periodic
+    // Nothing to copy and no rank exchanges in this call (e.g. one rank, nothing periodic): no launch.  A rank that
+    // has nothing to copy while others exchange still launches: the exchange epoch advances on every rank alike.
+    if (plan->tiles.empty() && !plan->global_active) return IGG_OK;
     if (plan->n_flags > (uint32_t)kMaxFlags)
         return fail(IGG_ERR_ARG, "update_halo: this call needs %u arrival flags, the control segment holds %d; split the call.",
                     plan->n_flags, kMaxFlags);
@@ -504,43 +627,115 @@ static int launch_exchange(igg_ctx* ctx, int nfields, const igg_field* fields, i
     }
 
     KParams p;
-    std::memset(&p, 0, sizeof(p));
     p.tiles = plan->d_tiles;
     p.n_tiles = (int32_t)plan->tiles.size();
     p.n_push_tiles = plan->n_push_tiles;
-    for (int i = 0; i < nfields; ++i) p.field[i] = fields[i].ptr;
+    p.plan = plan->active_mask ? plan->d_plan : nullptr;
+    // Epoch + staging parity live on the device.  A call in which no rank exchanges with another one (one rank, or
+    // only self-wrapped dimensions updated: the same verdict on every rank) needs neither and skips the prologue.
+    DeviceState* state = reinterpret_cast<DeviceState*>(ctx->ctrl);
+    p.state = plan->global_active ? state : nullptr;
     p.local_flags = reinterpret_cast<const unsigned long long*>(ctx->ctrl + kFlagsOff);
-    p.state = reinterpret_cast<DeviceState*>(ctx->ctrl);       // epoch + staging parity live on the device
-    p.active_mask = plan->active_mask;
-    p.unpack_half = ctx->staging_half;
     p.status = ctx->d_status;
     p.timeout_ns = ctx->timeout_ns;
-    for (int oi = 0; oi < IGG_NOFFSETS; ++oi) {
-        if (!((plan->active_mask >> oi) & 1u)) continue;
-        const Peer& peer = ctx->peers[plan->peer[oi]];
-        // The tiles carry offsets / flag numbers of the plan's own packed layout; shift every offset's base to that
-        // offset's region (same table on every rank).  What I push at offset oi lands in the receiver's region of
-        // the opposite offset.
-        const int ro = opposite_index(oi);
-        p.push_base[oi] = peer.staging.ptr + (ctx->region_off[ro] - plan->region_pack[ro]);
-        p.push_half[oi] = peer.staging.bytes;
-        p.unpack_base[oi] = ctx->staging + (ctx->region_off[oi] - plan->region_pack[oi]);
-        p.remote_flags[oi] = reinterpret_cast<unsigned long long*>(peer.ctrl.ptr + kFlagsOff) +
-                             ((long long)ctx->flag_off[ro] - (long long)plan->flag_pack[ro]);
-        p.local_flag_delta[oi] = (int32_t)((long long)ctx->flag_off[oi] - (long long)plan->flag_pack[oi]);
+    p.trace = nullptr;
+    p.notify = nullptr;
+    p.notify_value = 0;
+    p.fin_counter = &state->blocks_finished;
+    static const bool wx_params = !(std::getenv("IGG_WX_PARAMS") && std::atoi(std::getenv("IGG_WX_PARAMS")) == 0);
+    // (Measured and dropped: letting the WRAPX blocks sleep 400-1200 ns so that the contiguous tiles' loads get out
+    // before the strided flood -- 8.62 / 8.76 / 9.01 us against 8.64 us per cfg2 update, cold L2.)
+    p.wx_first = plan->wx_first;
+    p.wx_count = 0;
+    p.n_wx_ops = 0;
+    if (wx_params && plan->wx_count > 0 && plan->wx_ops.size() <= (size_t)kMaxWxOps) {
+        p.wx_count = plan->wx_count;
+        p.n_wx_ops = (int32_t)plan->wx_ops.size();
+        for (int k = 0; k < p.n_wx_ops; ++k) p.wx[k] = plan->wx_ops[k];
     }
+    p.copy_dst[0] = p.copy_dst[1] = nullptr;
+    p.copy_src[0] = p.copy_src[1] = nullptr;
+    for (int i = 0; i < nfields; ++i) p.field[i] = fields[i].ptr;
+    for (int i = nfields; i < IGG_MAX_FIELDS; ++i) p.field[i] = nullptr;
     order_after_previous(ctx, stream);
     if (ctx->d_trace) {
         p.trace = ctx->d_trace;
         ctx->last_grid = plan->grid;
         CU(cudaMemsetAsync(ctx->d_trace, 0, (size_t)ctx->max_blocks * 8 * sizeof(unsigned long long), stream));
     }
+    unsigned long long ticket = 0;
+    if (sync && ctx->spin_wait && !join_side) {
+        ticket = ++ctx->ticket;
+        p.notify = ctx->d_done;
+        p.notify_value = ticket;
+    }
     rc = launch_halo_kernel(p, plan->grid, stream, plan->ll128);
     if (join_side) CU(cudaStreamWaitEvent(stream, ctx->ev_join, 0));   // the call is complete when both kernels are
     if (rc) return rc;
     remember_launch(ctx, stream);
+    if (ticket) {
+        *waited = true;
+        return wait_done(ctx, stream, ticket);
+    }
     return IGG_OK;
 }
+
+// The fused single-phase exchange for the dimensions in `dims_mask` (plan lookup, staging growth, one launch).
+static int launch_exchange(igg_ctx* ctx, int nfields, const igg_field* fields, int dims_mask, cudaStream_t stream,
+                           const uint8_t* host_lines, bool sync, bool* waited) {
+    int rc;
+    Plan* plan = find_or_build_plan(ctx, nfields, fields, dims_mask, host_lines, &rc);
+    if (!plan) return rc;
+    if (!plan->pinned) {
+        // A launch recorded into a CUDA graph keeps pointing at the plan's device tables: never evict such a plan.
+        cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+        if (cudaStreamIsCapturing(stream, &cs) == cudaSuccess && cs != cudaStreamCaptureStatusNone) plan->pinned = true;
+        else cudaGetLastError();
+    }
+    return launch_plan(ctx, plan, nfields, fields, stream, sync, waited);
+}
+
+static int resolve_fields(igg_ctx* ctx, int nfields, const igg_field* fields_in, igg_field* fields, uint8_t* host_lines) {
+    static const bool host_lines_enabled = !(std::getenv("IGG_HOST_LINES") && std::atoi(std::getenv("IGG_HOST_LINES")) == 0);
+    for (int i = 0; i < nfields; ++i) {
+        fields[i] = fields_in[i];
+        bool is_host = false;
+        int rc = resolve_pointer(ctx, fields_in[i].ptr, &fields[i].ptr, &is_host);
+        if (rc) return rc;
+        // Fields in page-locked host memory: whole-line x self-wrap (kOpWrapLines) unless IGG_HOST_LINES=0.
+        host_lines[i] = (is_host && host_lines_enabled && (uintptr_t)fields[i].ptr % 64 == 0) ? 1 : 0;
+    }
+    return IGG_OK;
+}
+
+// Comparison path: the reference's dependent phases, in the caller's order (default z, x, y).
+static int nccl_update(igg_ctx* ctx, int nfields, const igg_field* fields, const uint8_t* host_lines, const int* dims_order,
+                       int ndims_order, cudaStream_t stream) {
+    static const int kDefaultOrder[3] = {3, 1, 2};
+    const int* order = (dims_order && ndims_order > 0) ? dims_order : kDefaultOrder;
+    const int norder = (dims_order && ndims_order > 0) ? ndims_order : 3;
+    KParams proto;
+    std::memset(&proto, 0, sizeof(proto));
+    proto.local_flags = reinterpret_cast<const unsigned long long*>(ctx->ctrl + kFlagsOff);
+    proto.status = ctx->d_status;
+    proto.timeout_ns = ctx->timeout_ns;
+    order_after_previous(ctx, stream);
+    for (int q = 0; q < norder; ++q) {
+        const int d = order[q] - 1;
+        const int64_t l = ctx->g.neighbors[d][0], r = ctx->g.neighbors[d][1];
+        if (l < 0 && r < 0) continue;
+        int rc;
+        bool waited;
+        if (l == ctx->g.me && r == ctx->g.me) rc = launch_exchange(ctx, nfields, fields, 1 << d, stream, host_lines, false, &waited);   // local wrap
+        else rc = nccl_phase(ctx->nccl, ctx->g, nfields, fields, d, ctx->max_blocks, proto, stream, &ctx->launches);
+        if (rc) return rc;
+    }
+    ctx->last_stream = stream;
+    ctx->have_last = true;
+    return IGG_OK;
+}
+
+extern "C" {
 
 int igg_update_halo(igg_ctx* ctx, int nfields, const igg_field* fields_in, const int* dims_order, int ndims_order,
                     void* stream_v, int flags) {
@@ -552,49 +747,147 @@ int igg_update_halo(igg_ctx* ctx, int nfields, const igg_field* fields_in, const
     if (rc) return rc;
     rc = check_fields(ctx->g, nfields, fields_in);
     if (rc) return rc;
-    CU(cudaSetDevice(ctx->device));
+    rc = check_status(ctx);
+    if (rc) return rc;
+    rc = make_current(ctx);
+    if (rc) return rc;
 
     igg_field fields[IGG_MAX_FIELDS];
     uint8_t host_lines[IGG_MAX_FIELDS];
-    static const bool host_lines_enabled = !(std::getenv("IGG_HOST_LINES") && std::atoi(std::getenv("IGG_HOST_LINES")) == 0);
-    for (int i = 0; i < nfields; ++i) {
-        fields[i] = fields_in[i];
-        bool is_host = false;
-        rc = resolve_pointer(ctx, fields_in[i].ptr, &fields[i].ptr, &is_host);
-        if (rc) return rc;
-        // Fields in page-locked host memory: whole-line x self-wrap (kOpWrapLines) unless IGG_HOST_LINES=0.
-        host_lines[i] = (is_host && host_lines_enabled && (uintptr_t)fields[i].ptr % 64 == 0) ? 1 : 0;
-    }
+    rc = resolve_fields(ctx, nfields, fields_in, fields, host_lines);
+    if (rc) return rc;
 
+    const bool sync = !(flags & IGG_ASYNC);
+    bool waited = false;
+    if (ctx->mode == IGG_MODE_NCCL_3PHASE && ctx->g.nprocs > 1) rc = nccl_update(ctx, nfields, fields, host_lines, dims_order, ndims_order, stream);
+    else rc = launch_exchange(ctx, nfields, fields, dims_mask, stream, host_lines, sync, &waited);
+    if (rc) return rc;
+    if (sync && !waited) return wait_done(ctx, stream, 0);
+    return IGG_OK;
+}
+
+int igg_prepare(igg_ctx* ctx, int nfields, const igg_field* fields_in, const int* dims_order, int ndims_order,
+                igg_prepared** out) {
+    if (!ctx || !fields_in || !out) return fail(IGG_ERR_ARG, "igg_prepare: NULL argument.");
+    if (!ctx->bootstrapped) return fail(IGG_ERR_STATE, "igg_prepare: call igg_bootstrap_import first (nprocs > 1).");
+    if (ndims_order > 3) return fail(IGG_ERR_ARG, "igg_prepare: at most 3 entries in dims.");
+    std::unique_ptr<igg_prepared> h(new igg_prepared());
+    int rc = dims_mask_from_order(dims_order, ndims_order, &h->dims_mask);
+    if (rc) return rc;
+    rc = check_fields(ctx->g, nfields, fields_in);
+    if (rc) return rc;
+    rc = make_current(ctx);
+    if (rc) return rc;
+    h->ctx = ctx;
+    h->nfields = nfields;
+    if (dims_order && ndims_order > 0) { h->ndims_order = ndims_order; for (int i = 0; i < ndims_order; ++i) h->dims_order[i] = dims_order[i]; }
+    for (int i = 0; i < nfields; ++i) h->user_fields[i] = fields_in[i];
+    rc = resolve_fields(ctx, nfields, fields_in, h->fields, h->host_lines);
+    if (rc) return rc;
+    // Building the plan here allocates its device tables now, not in the time loop.  (Staging for exchanges between
+    // ranks still grows at the first call that needs it: that step is collective.)
+    h->plan = find_or_build_plan(ctx, nfields, h->fields, h->dims_mask, h->host_lines, &rc);
+    if (!h->plan) return rc;
+    h->plan->pinned = true;
+    h->mode = ctx->mode;
+    ctx->prepared.push_back(h.get());
+    *out = h.release();
+    return IGG_OK;
+}
+
+int igg_update_halo_prepared(igg_prepared* h, void* stream_v, int flags) {
+    if (!h) return fail(IGG_ERR_ARG, "igg_update_halo_prepared: NULL handle.");
+    igg_ctx* ctx = h->ctx;
+    if (!ctx) return fail(IGG_ERR_STATE, "igg_update_halo_prepared: the context of this prepared call has been destroyed.");
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_v);
+    int rc = check_status(ctx);
+    if (rc) return rc;
+    rc = make_current(ctx);
+    if (rc) return rc;
+    const bool sync = !(flags & IGG_ASYNC);
+    bool waited = false;
     if (ctx->mode == IGG_MODE_NCCL_3PHASE && ctx->g.nprocs > 1) {
-        // Comparison path: the reference's dependent phases, in the caller's order (default z, x, y).
-        static const int kDefaultOrder[3] = {3, 1, 2};
-        const int* order = (dims_order && ndims_order > 0) ? dims_order : kDefaultOrder;
-        const int norder = (dims_order && ndims_order > 0) ? ndims_order : 3;
-        KParams proto;
-        std::memset(&proto, 0, sizeof(proto));
-        proto.local_flags = reinterpret_cast<const unsigned long long*>(ctx->ctrl + kFlagsOff);
-        proto.status = ctx->d_status;
-        proto.timeout_ns = ctx->timeout_ns;
-        order_after_previous(ctx, stream);
-        for (int q = 0; q < norder; ++q) {
-            const int d = order[q] - 1;
-            const int64_t l = ctx->g.neighbors[d][0], r = ctx->g.neighbors[d][1];
-            if (l < 0 && r < 0) continue;
-            if (l == ctx->g.me && r == ctx->g.me) rc = launch_exchange(ctx, nfields, fields, 1 << d, stream, host_lines);   // local wrap
-            else rc = nccl_phase(ctx->nccl, ctx->g, nfields, fields, d, ctx->max_blocks, proto, stream, &ctx->launches);
-            if (rc) return rc;
-        }
-        ctx->last_stream = stream;
-        ctx->have_last = true;
+        rc = nccl_update(ctx, h->nfields, h->fields, h->host_lines, h->dims_order, h->ndims_order, stream);
     } else {
-        rc = launch_exchange(ctx, nfields, fields, dims_mask, stream, host_lines);
+        if (h->mode != ctx->mode) {            // the exchange mode changed since: the plan of the new mode
+            h->plan = find_or_build_plan(ctx, h->nfields, h->fields, h->dims_mask, h->host_lines, &rc);
+            if (!h->plan) return rc;
+            h->plan->pinned = true;
+            h->mode = ctx->mode;
+        }
+        rc = launch_plan(ctx, h->plan, h->nfields, h->fields, stream, sync, &waited);
+    }
+    if (rc) return rc;
+    if (sync && !waited) return wait_done(ctx, stream, 0);
+    return IGG_OK;
+}
+
+// Host cost of issuing `n` stream-ordered prepared calls from C (no foreign-call overhead in between): ns per call.
+int igg_debug_issue_loop(igg_prepared* h, void* stream, int n, double* ns_per_call_out) {
+    if (!h || !ns_per_call_out || n < 1) return fail(IGG_ERR_ARG, "igg_debug_issue_loop: invalid argument.");
+    timespec a, b;
+    clock_gettime(CLOCK_MONOTONIC, &a);
+    for (int i = 0; i < n; ++i) {
+        const int rc = igg_update_halo_prepared(h, stream, IGG_ASYNC);
         if (rc) return rc;
     }
+    clock_gettime(CLOCK_MONOTONIC, &b);
+    *ns_per_call_out = ((b.tv_sec - a.tv_sec) * 1e9 + (b.tv_nsec - a.tv_nsec)) / n;
+    return IGG_OK;
+}
+
+// The timed loop of a compiled-language caller (what a Julia time loop over `ccall`s would be): `steps` prepared calls,
+// call i using calls[i % ncalls].  IGG_ASYNC: every call sits between its own pair of CUDA events on `stream`
+// (us_out[i] = event time of call i, *loop_us_out = first event to last event / steps).  IGG_SYNC: host clock around
+// every host-synchronous call.
+int igg_debug_timed_calls(igg_prepared** calls, int ncalls, void* stream_v, int steps, int flags, float* us_out,
+                          double* loop_us_out) {
+    if (!calls || ncalls < 1 || steps < 1 || !us_out) return fail(IGG_ERR_ARG, "igg_debug_timed_calls: invalid argument.");
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_v);
     if (!(flags & IGG_ASYNC)) {
-        CU(cudaStreamSynchronize(stream));
-        return check_status(ctx);
+        for (int i = 0; i < steps; ++i) {
+            timespec a, b;
+            clock_gettime(CLOCK_MONOTONIC, &a);
+            const int rc = igg_update_halo_prepared(calls[i % ncalls], stream_v, IGG_SYNC);
+            clock_gettime(CLOCK_MONOTONIC, &b);
+            if (rc) return rc;
+            us_out[i] = (float)(((b.tv_sec - a.tv_sec) * 1e9 + (b.tv_nsec - a.tv_nsec)) * 1e-3);
+        }
+        if (loop_us_out) *loop_us_out = 0;
+        return IGG_OK;
     }
+    std::vector<cudaEvent_t> ev(2 * (size_t)steps, nullptr);
+    int rc = IGG_OK;
+    for (auto& e : ev)
+        if (cudaEventCreate(&e) != cudaSuccess) rc = fail(IGG_ERR_CUDA, "igg_debug_timed_calls: cudaEventCreate failed.");
+    for (int i = 0; i < steps && !rc; ++i) {
+        cudaEventRecord(ev[2 * i], stream);
+        rc = igg_update_halo_prepared(calls[i % ncalls], stream_v, IGG_ASYNC);
+        cudaEventRecord(ev[2 * i + 1], stream);
+    }
+    if (!rc && cudaStreamSynchronize(stream) != cudaSuccess) rc = fail(IGG_ERR_CUDA, "igg_debug_timed_calls: %s", cudaGetErrorString(cudaGetLastError()));
+    if (!rc) {
+        for (int i = 0; i < steps; ++i) {
+            float ms = 0;
+            cudaEventElapsedTime(&ms, ev[2 * i], ev[2 * i + 1]);
+            us_out[i] = ms * 1e3f;
+        }
+        float ms = 0;
+        cudaEventElapsedTime(&ms, ev[0], ev[2 * (size_t)steps - 1]);
+        if (loop_us_out) *loop_us_out = ms * 1e3 / steps;
+    }
+    for (auto& e : ev) if (e) cudaEventDestroy(e);
+    return rc;
+}
+
+int igg_release_prepared(igg_prepared* h) {
+    if (!h) return IGG_OK;
+    if (h->ctx) {
+        auto& v = h->ctx->prepared;
+        for (size_t k = 0; k < v.size(); ++k)
+            if (v[k] == h) { v.erase(v.begin() + (long)k); break; }
+    }
+    delete h;      // its plan stays cached (and pinned: a captured graph may refer to it) until the context goes
     return IGG_OK;
 }
 
@@ -724,7 +1017,7 @@ int igg_gather(igg_ctx* ctx, const void* A, const int64_t sizeA_in[3], int ndims
     p.n_tiles = (int32_t)tiles.size();
     p.n_push_tiles = 0;
     p.field[0] = const_cast<char*>(src);
-    p.push_base[0] = dst_base;
+    p.copy_dst[0] = dst_base;
     p.local_flags = reinterpret_cast<const unsigned long long*>(ctx->ctrl + kFlagsOff);
     p.status = ctx->d_status;
     p.timeout_ns = ctx->timeout_ns;
@@ -793,7 +1086,8 @@ int igg_nccl_init(igg_ctx* ctx, const void* id) {
 
 int64_t igg_launch_count(const igg_ctx* ctx) { return ctx ? ctx->launches : 0; }
 const char* igg_kernel_name(void) {
-    // the kernel a new context launches: LL128 unless IGG_MODE selects the fence protocol (as in igg_create)
+    // The kernel a new context launches for calls below the bulk threshold (all single-rank calls): the LL128
+    // instantiation unless IGG_MODE selects the fence protocol (as in igg_create).  Same body, see halo_kernel.cu.
     const char* m = getenv("IGG_MODE");
     const bool fence = m && (!strcmp(m, "fence") || !strcmp(m, "ipc"));
     return fence ? halo_kernel_name() : "igg_halo_exchange_ll128_kernel";

@@ -2,10 +2,13 @@
 //
 // One launch per update_halo call does, for all fields and all 26 neighbour offsets:
 //   PUSH   pack a send box of my field and store it straight into the neighbour GPU's staging slot through its
-//          CUDA-IPC peer mapping (NVLink); each 8-KiB tile is released on its own: barrier, fence.acq_rel.sys, then
-//          the call's epoch is stored into that tile's arrival flag on the neighbour.
-//   LOCAL  periodic wrap inside my own array (the rank is its own neighbour): send box -> opposite receive box.
-//   UNPACK wait for the tile's arrival flag (ld.acquire.sys), then copy the staged tile into my receive box.
+//          CUDA-IPC peer mapping (NVLink).  Two ways, chosen per plan (igg_internal.h, kProto*):
+//            LL128 (latency regime)   staging lines of 120 payload bytes + the call's 8-byte epoch, no fence, no flag;
+//            fence (bandwidth regime) 16-byte loads / stores, tiles of up to 128 KiB, each released on its own:
+//                                     barrier, fence.acq_rel.sys, then the epoch goes into the tile's arrival flag.
+//   LOCAL  periodic wrap inside my own array (the rank is its own neighbour): send box -> opposite receive box;
+//   WRAPX  the same for the two x-faces of a field, one thread per row doing both directions (strided cells).
+//   UNPACK wait for the tile's lines (LL128) or arrival flag (ld.acquire.sys), then copy it into my receive box.
 // It replaces the reference's write_d2x! / read_x2d! kernels, the cuMemcpy3DAsync staging copies, the D2D
 // self-copy and the 12 host-blocking stream synchronisations per field
 // (ref: src/CUDAExt/update_halo.jl:153-259, src/update_halo.jl:51-88).
@@ -15,8 +18,9 @@
 // The grid never exceeds the number of co-resident blocks, so spinning blocks cannot starve pushing ones.
 //
 // Pure data movement: bytes are copied as opaque 1/2/4/8/16-byte words, so results are bit-exact for any element
-// type.  No tensor cores, no shared-memory staging: each tile row is a contiguous run in both source and
-// destination, and strided x-faces degenerate to one element per row (inherent 32-byte-sector granularity).
+// type.  No tensor cores.  Each copy-tile row is a contiguous run in both source and destination; strided x-faces
+// degenerate to one element per row, and what they cost is DRAM's 128-byte line per cell in both directions
+// (profiles/xface_floor.cu), not instructions.
 #include <cuda_runtime.h>
 
 #include <cstdlib>
@@ -47,17 +51,10 @@ __device__ __forceinline__ unsigned long long globaltimer_ns() {
     return t;
 }
 
-// Loads.  Field data was written by earlier kernels of this stream: default caching, no L1 allocation (streamed
-// once).  Staging data is written by a peer GPU during this kernel: read it at L2 (ld.cg), the point of coherence.
-// LM selects the load flavour for field data: 0 = ld.global.cs, 1 = plain ld.global (used), 2 = ld.global.nc,
-// 3 = ld.global.cg.  Measured on cfg2, cold L2: .cs 12.5 us per update, plain / .nc / .cg 9.6 us; every flavour makes
-// L2 fetch the whole 128-byte line of a strided x-face cell (595 k L2 read sectors for 222 k requested).
-template <typename V, int LM> __device__ __forceinline__ V load_stream(const V* p) {
-    if (LM == 0) return __ldcs(p);
-    if (LM == 2) return __ldg(p);
-    if (LM == 3) return __ldcg(p);
-    return *p;
-}
+// Loads.  Field data was written by earlier kernels of this stream: plain loads (measured on cfg2, cold L2: .cs
+// 12.5 us per update, plain / .nc / .cg 9.6 us).  Staging data is written by a peer GPU during this kernel: read it
+// at L2 (ld.cg), the point of coherence.
+template <typename V> __device__ __forceinline__ V load_stream(const V* p) { return *p; }
 template <typename V> __device__ __forceinline__ V load_l2(const V* p) { return __ldcg(p); }
 template <> __device__ __forceinline__ unsigned char load_l2(const unsigned char* p) {
     return *reinterpret_cast<const volatile unsigned char*>(p);
@@ -90,6 +87,24 @@ __device__ __forceinline__ TileRec load_tile(const TileRec* g) {
     return t;
 }
 
+// Tile `ti` of the launch: derived from the kernel parameters if it is one of the WRAPX tiles described there, else
+// loaded from the table.  (The choice is uniform over the block.)
+__device__ __forceinline__ TileRec get_tile(const KParams& p, int ti) {
+    const int j = ti - p.wx_first;
+    if (j >= 0 && j < p.wx_count) {
+        int k = 0;
+        while (k + 1 < p.n_wx_ops && (uint32_t)j >= p.wx[k + 1].tile0) ++k;
+        const WrapXOp& w = p.wx[k];
+        TileRec t;
+        t.src_off = w.src_off; t.dst_off = w.dst_off; t.src_sy = w.sy; t.src_sz = w.sz; t.dst_sy = w.delta; t.dst_sz = 0;
+        t.row0 = ((uint32_t)j - w.tile0) * w.rows_per_tile;
+        t.nrows = min(w.rows_per_tile, w.rows - t.row0);
+        t.ncols = w.ncols; t.ny = w.ny; t.field = w.field; t.vec_log2 = w.vec_log2; t.kind = (uint8_t)kOpWrapX; t.nbr = 0; t.flag_idx = 0;
+        return t;
+    }
+    return load_tile(p.tiles + ti);
+}
+
 // Byte offsets of item i of a tile: i -> (row r = i / ncols, column c = i % ncols) -> (y, z) of the flattened row.
 template <typename V>
 __device__ __forceinline__ void item_offsets(const TileRec& t, uint32_t i, int64_t& soff, int64_t& doff) {
@@ -105,7 +120,7 @@ __device__ __forceinline__ void item_offsets(const TileRec& t, uint32_t i, int64
 
 // Copies one tile; all loads of an unrolled group are issued before the first store (offsets are recomputed for
 // the stores instead of being kept live, which keeps the kernel within 64 registers = 4 blocks per SM).
-template <typename V, bool FROM_STAGING, int LM>
+template <typename V, bool FROM_STAGING>
 __device__ __forceinline__ void copy_tile(const TileRec& t, const char* __restrict__ src, char* __restrict__ dst) {
     constexpr int kUnroll = Unroll<V>::value;
     const uint32_t items = t.ncols * t.nrows;
@@ -120,7 +135,7 @@ __device__ __forceinline__ void copy_tile(const TileRec& t, const char* __restri
                 int64_t soff, doff;
                 item_offsets<V>(t, i, soff, doff);
                 const V* sp = reinterpret_cast<const V*>(src + soff);
-                v[u] = FROM_STAGING ? load_l2<V>(sp) : load_stream<V, LM>(sp);
+                v[u] = FROM_STAGING ? load_l2<V>(sp) : load_stream<V>(sp);
             }
         }
 #pragma unroll
@@ -135,14 +150,62 @@ __device__ __forceinline__ void copy_tile(const TileRec& t, const char* __restri
     }
 }
 
-template <bool FROM_STAGING, int LM>
+template <bool FROM_STAGING>
 __device__ __forceinline__ void copy_tile_dispatch(const TileRec& t, const char* src, char* dst) {
     switch (t.vec_log2) {
-        case 4: copy_tile<uint4, FROM_STAGING, LM>(t, src, dst); break;
-        case 3: copy_tile<uint2, FROM_STAGING, LM>(t, src, dst); break;
-        case 2: copy_tile<unsigned int, FROM_STAGING, LM>(t, src, dst); break;
-        case 1: copy_tile<unsigned short, FROM_STAGING, LM>(t, src, dst); break;
-        default: copy_tile<unsigned char, FROM_STAGING, LM>(t, src, dst); break;
+        case 4: copy_tile<uint4, FROM_STAGING>(t, src, dst); break;
+        case 3: copy_tile<uint2, FROM_STAGING>(t, src, dst); break;
+        case 2: copy_tile<unsigned int, FROM_STAGING>(t, src, dst); break;
+        case 1: copy_tile<unsigned short, FROM_STAGING>(t, src, dst); break;
+        default: copy_tile<unsigned char, FROM_STAGING>(t, src, dst); break;
+    }
+}
+
+// kOpWrapX: periodic x self-wrap, one thread per (row, word), both directions at once.  The four accesses of a row
+// touch two 32-byte sectors (send cell and halo cell are neighbours at either end of the row).
+// Strided single words: ask L2 for 64 bytes, not for the whole 128-byte line (the default L1 fill requests all four
+// sectors: 524 k sector reads for 131 k cells; with the hint 262 k, profiles/xface_floor.cu: 3.4 -> 2.6 us L2-hot).
+__device__ __forceinline__ unsigned long long ld_strided(const unsigned long long* p) {
+    unsigned long long v;
+    asm volatile("ld.global.L2::64B.u64 %0, [%1];" : "=l"(v) : "l"(p));
+    return v;
+}
+template <typename V> __device__ __forceinline__ V ld_strided(const V* p) { return *p; }
+template <> __device__ __forceinline__ uint2 ld_strided(const uint2* p) {
+    const unsigned long long v = ld_strided(reinterpret_cast<const unsigned long long*>(p));
+    return make_uint2((unsigned)v, (unsigned)(v >> 32));
+}
+template <> __device__ __forceinline__ unsigned int ld_strided(const unsigned int* p) {
+    unsigned int v;
+    asm volatile("ld.global.L2::64B.u32 %0, [%1];" : "=r"(v) : "l"(p));
+    return v;
+}
+
+// One item per thread and pass (more rows per thread measured no faster: profiles/xface_floor.cu, r1 / r2 / r4).
+template <typename V>
+__device__ __forceinline__ void wrapx_tile(const TileRec& t, char* __restrict__ base) {
+    const uint32_t items = t.ncols * t.nrows;
+    for (uint32_t i = threadIdx.x; i < items; i += kThreads) {
+        uint32_t r = i, c = 0;
+        if (t.ncols != 1) { r = i / t.ncols; c = i - r * t.ncols; }
+        const uint32_t row = t.row0 + r;
+        uint32_t z = 0, y = row;
+        if (row >= t.ny) { z = row / t.ny; y = row - z * t.ny; }
+        char* lo_send = base + t.src_off + ((int64_t)y * t.src_sy + (int64_t)z * t.src_sz + (int64_t)c * (int64_t)sizeof(V));
+        char* hi_halo = lo_send + (t.dst_off - t.src_off);
+        const V a = ld_strided(reinterpret_cast<const V*>(lo_send));
+        const V b = ld_strided(reinterpret_cast<const V*>(hi_halo - t.dst_sy));
+        *reinterpret_cast<V*>(hi_halo) = a;
+        *reinterpret_cast<V*>(lo_send - t.dst_sy) = b;
+    }
+}
+__device__ __forceinline__ void wrapx_tile_dispatch(const TileRec& t, char* base) {
+    switch (t.vec_log2) {
+        case 4: wrapx_tile<uint4>(t, base); break;
+        case 3: wrapx_tile<uint2>(t, base); break;
+        case 2: wrapx_tile<unsigned int>(t, base); break;
+        case 1: wrapx_tile<unsigned short>(t, base); break;
+        default: wrapx_tile<unsigned char>(t, base); break;
     }
 }
 
@@ -196,18 +259,20 @@ __device__ __forceinline__ void ld_volatile_v2(const char* p, unsigned long long
     asm volatile("ld.volatile.global.v2.u64 {%0, %1}, [%2];" : "=l"(lo), "=l"(hi) : "l"(p) : "memory");
 }
 
-// Position of payload byte `pb` of a box inside the field: merged rows of `rowb` bytes, ny rows per plane.
+// Position of payload byte `pb` of a box inside the field: merged rows of `rowb` bytes, ny rows per plane.  32-bit
+// index arithmetic: a staging slot is smaller than 4 GiB (checked when the plan is built).
 struct BoxCursor {
     int64_t off;          // byte offset from the box origin in the field
     uint32_t c, y;        // byte within the row, row within the plane
 };
-__device__ __forceinline__ BoxCursor box_seek(int64_t pb, uint32_t rowb, uint32_t ny, int64_t sy, int64_t sz) {
-    const int64_t r = pb / rowb;
+__device__ __forceinline__ BoxCursor box_seek(uint32_t pb, uint32_t rowb, uint32_t ny, int64_t sy, int64_t sz) {
     BoxCursor k;
-    k.c = (uint32_t)(pb - r * rowb);
-    const int64_t z = r / ny;
-    k.y = (uint32_t)(r - z * ny);
-    k.off = (int64_t)k.y * sy + z * sz + k.c;
+    uint32_t r = 0, z = 0;
+    k.c = pb;
+    if (pb >= rowb) { r = pb / rowb; k.c = pb - r * rowb; }
+    k.y = r;
+    if (r >= ny) { z = r / ny; k.y = r - z * ny; }
+    k.off = (int64_t)k.y * sy + (int64_t)z * sz + k.c;
     return k;
 }
 template <int W>
@@ -224,31 +289,45 @@ template <> struct WordOf<2> { typedef unsigned short T; };
 template <> struct WordOf<4> { typedef unsigned int T; };
 template <> struct WordOf<8> { typedef unsigned long long T; };
 
+static_assert(kLinesPerTile == 2 * (kThreads / 8), "an LL128 tile is two passes of the block");
+
 // PUSH: pack the lines [row0, row0 + nrows) of a slot and store them into the neighbour's staging, 8 lanes per line.
+// Both passes of the tile load before either stores (four 8-byte loads in flight per lane).
 template <int W>
 __device__ __forceinline__ void push_ll_tile(const TileRec& t, const char* __restrict__ box, char* __restrict__ slot,
                                              unsigned long long epoch) {
     typedef typename WordOf<W>::T Wt;
-    const uint32_t j = threadIdx.x & 7u;
-    for (uint32_t g = threadIdx.x >> 3; g < t.nrows; g += kThreads / 8) {
-        const int64_t line = (int64_t)t.row0 + g;
-        const int64_t pb = line * kLinePayload + 16 * j;
-        int nb = j == 7 ? 8 : 16;
-        if (pb + nb > t.dst_sy) nb = t.dst_sy > pb ? (int)(t.dst_sy - pb) : 0;
-        unsigned long long v[2] = {0ull, 0ull};
-        if (nb > 0) {
-            BoxCursor k = box_seek(pb, t.ncols, t.ny, t.src_sy, t.src_sz);
+    const uint32_t j = threadIdx.x & 7u, g0 = threadIdx.x >> 3;
+    const uint32_t nbytes = (uint32_t)t.dst_sy;
+    unsigned long long v[2][2];
 #pragma unroll
-            for (int b = 0; b < 16; b += W) {
-                if (b < nb) {
-                    const unsigned long long w = *reinterpret_cast<const Wt*>(box + k.off);
-                    v[b >> 3] |= w << (8 * (b & 7));
-                    box_step<W>(k, t.ncols, t.ny, t.src_sy, t.src_sz);
+    for (int u = 0; u < 2; ++u) {
+        const uint32_t g = g0 + u * (kThreads / 8);
+        v[u][0] = v[u][1] = 0ull;
+        if (g < t.nrows) {
+            const uint32_t pb = (t.row0 + g) * kLinePayload + 16u * j;
+            int nb = j == 7 ? 8 : 16;
+            if (pb + nb > nbytes) nb = nbytes > pb ? (int)(nbytes - pb) : 0;
+            if (nb > 0) {
+                BoxCursor k = box_seek(pb, t.ncols, t.ny, t.src_sy, t.src_sz);
+#pragma unroll
+                for (int b = 0; b < 16; b += W) {
+                    if (b < nb) {
+                        const unsigned long long w = *reinterpret_cast<const Wt*>(box + k.off);
+                        v[u][b >> 3] |= w << (8 * (b & 7));
+                        box_step<W>(k, t.ncols, t.ny, t.src_sy, t.src_sz);
+                    }
                 }
             }
         }
-        if (j == 7) v[1] = epoch;
-        st_volatile_v2(slot + line * 128 + 16 * j, v[0], v[1]);
+    }
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+        const uint32_t g = g0 + u * (kThreads / 8);
+        if (g < t.nrows) {
+            if (j == 7) v[u][1] = epoch;
+            st_volatile_v2(slot + (int64_t)(t.row0 + g) * 128 + 16 * j, v[u][0], v[u][1]);
+        }
     }
 }
 
@@ -259,12 +338,13 @@ __device__ __forceinline__ bool unpack_ll_tile(const TileRec& t, char* __restric
                                                unsigned long long epoch, unsigned long long timeout_ns) {
     typedef typename WordOf<W>::T Wt;
     const uint32_t j = threadIdx.x & 7u, lane = threadIdx.x & 31u;
+    const uint32_t nbytes = (uint32_t)t.dst_sy;
     const uint32_t passes = (t.nrows + kThreads / 8 - 1) / (kThreads / 8);
     for (uint32_t ps = 0; ps < passes; ++ps) {                 // every lane runs every pass (warp-wide votes below)
         const uint32_t g = ps * (kThreads / 8) + (threadIdx.x >> 3);
         const bool on = g < t.nrows;
-        const int64_t line = (int64_t)t.row0 + g;
-        const char* src = slot + line * 128 + 16 * j;
+        const uint32_t line = t.row0 + g;
+        const char* src = slot + (int64_t)line * 128 + 16 * j;
         unsigned long long v[2] = {0ull, 0ull};
         unsigned long long t0 = 0;
         unsigned int spins = 0;
@@ -280,9 +360,9 @@ __device__ __forceinline__ bool unpack_ll_tile(const TileRec& t, char* __restric
             }
         }
         if (on) {
-            const int64_t pb = line * kLinePayload + 16 * j;
+            const uint32_t pb = line * kLinePayload + 16u * j;
             int nb = j == 7 ? 8 : 16;
-            if (pb + nb > t.dst_sy) nb = t.dst_sy > pb ? (int)(t.dst_sy - pb) : 0;
+            if (pb + nb > nbytes) nb = nbytes > pb ? (int)(nbytes - pb) : 0;
             if (nb > 0) {
                 BoxCursor k = box_seek(pb, t.ncols, t.ny, t.src_sy, t.src_sz);
 #pragma unroll
@@ -298,40 +378,47 @@ __device__ __forceinline__ bool unpack_ll_tile(const TileRec& t, char* __restric
     return true;
 }
 
-template <int LM, bool LL>
+template <bool LL>
 __device__ __forceinline__ void halo_exchange_body(const KParams& p) {
     __shared__ unsigned long long s_epoch;            // flag value of this launch (exchange launches so far + 1)
-    __shared__ unsigned int s_half[IGG_NOFFSETS];     // staging half (0/1) used with the neighbour at offset o
+    __shared__ char* s_push[IGG_NOFFSETS];            // staging half this launch stores into at the neighbour at offset o
+    __shared__ const char* s_unpack[IGG_NOFFSETS];    // staging half of mine the neighbour at offset o stores into
+    __shared__ unsigned long long* s_rflags[IGG_NOFFSETS];
+    __shared__ int s_lflag_delta[IGG_NOFFSETS];
     // Optional per-block timeline (igg_trace_enable): [0] globaltimer at start, then SM clock at [1] start,
     // [2] first tile record loaded, [3] first copy issued, [4] first push flagged, [5] first flag seen, [6] end.
 #define IGG_TRACE(k) do { if (p.trace && threadIdx.x == 0) p.trace[(size_t)blockIdx.x * 8 + (k)] = (unsigned long long)clock64(); } while (0)
     if (p.trace && threadIdx.x == 0) p.trace[(size_t)blockIdx.x * 8] = globaltimer_ns();
     IGG_TRACE(1);
 
-    int ti = blockIdx.x;                              // grid <= n_tiles, so the first tile always exists
-    TileRec t = load_tile(p.tiles + ti);              // in flight together with the state loads below
+    int ti = blockIdx.x;
+    TileRec t;
+    if (ti < p.n_tiles) t = get_tile(p, ti);          // in flight together with the state / plan loads below
+    else t.kind = 0xff;                               // a launch without tiles only advances the exchange state
     // Programmatic dependent launch: this grid may have been scheduled while the previous kernel of the stream was
     // still running (its launch latency is hidden); nothing that kernel wrote is touched before this point.
-    // (The tile table is immutable.)  A no-op when the launch carries no programmatic dependency.
+    // (The tile table and the plan constants are immutable.)  A no-op when the launch carries no programmatic dependency.
     asm volatile("griddepcontrol.wait;" ::: "memory");
     if (p.state) {
-        if (threadIdx.x < IGG_NOFFSETS) s_half[threadIdx.x] = (__ldcg(&p.state->exchanges[threadIdx.x]) + 1u) & 1u;
-        if (threadIdx.x == 32) s_epoch = __ldcg(&p.state->call_epoch) + 1ull;
-    } else if (threadIdx.x < IGG_NOFFSETS) {
-        s_half[threadIdx.x] = 0;
-    }
-    __syncthreads();
-    // Every block has now read the state it needs; the last block to get here advances it for the next launch
-    // (which is stream-ordered after this one).  Done early so that it is off the kernel's tail.
-    if (p.state && threadIdx.x == 0) {
-        const unsigned int seen = atomicAdd(&p.state->blocks_done, 1u);
-        if (seen == gridDim.x - 1) {
-            p.state->blocks_done = 0;
-            p.state->call_epoch = s_epoch;
-            for (int o = 0; o < IGG_NOFFSETS; ++o)
-                if ((p.active_mask >> o) & 1u) p.state->exchanges[o] += 1u;
+        if (threadIdx.x < IGG_NOFFSETS) {
+            const int o = threadIdx.x;
+            const long long half = (long long)((__ldcg(&p.state->exchanges[o]) + 1u) & 1u);
+            if (p.plan) {
+                s_push[o] = p.plan->push_base[o] + half * p.plan->push_half[o];
+                s_unpack[o] = p.plan->unpack_base[o] + half * p.plan->unpack_half;
+                s_rflags[o] = p.plan->remote_flags[o];
+                s_lflag_delta[o] = p.plan->local_flag_delta[o];
+            }
         }
+        if (threadIdx.x == 32) s_epoch = __ldcg(&p.state->call_epoch) + 1ull;
+        __syncthreads();
     }
+    // Every block has now read the state it needs and says so; the last block to have said so advances the state for
+    // the next launch (which is stream-ordered after this one) -- after its tiles, below: the count is issued here and
+    // its result is only looked at there, so that no warp waits for the atomic's round trip before its loads.
+    // (Launches that exchange with no other rank carry no state: nothing to read, no barrier, no count.)
+    unsigned int seen = 0;
+    if (p.state && threadIdx.x == 0) seen = atomicAdd(&p.state->blocks_done, 1u);
     // Let the next kernel of the stream begin its launch now; it cannot touch memory before this grid has completed
     // (it starts with griddepcontrol.wait, or it is an ordinary launch that waits for completion anyway).
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
@@ -341,10 +428,13 @@ __device__ __forceinline__ void halo_exchange_body(const KParams& p) {
     IGG_TRACE(2);
 
     bool first = true;
-    while (true) {
-        if (LL && t.kind == kOpPushLL) {
+    while (ti < p.n_tiles) {
+        if (t.kind == kOpWrapX) {
+            wrapx_tile_dispatch(t, static_cast<char*>(p.field[t.field]));
+            if (first) IGG_TRACE(3);
+        } else if (LL && t.kind == kOpPushLL) {
             const char* box = static_cast<const char*>(p.field[t.field]) + t.src_off;
-            char* slot = p.push_base[t.nbr] + (long long)s_half[t.nbr] * p.push_half[t.nbr] + t.dst_off;
+            char* slot = s_push[t.nbr] + t.dst_off;
             switch (t.vec_log2) {
                 case 3: push_ll_tile<8>(t, box, slot, s_epoch); break;
                 case 2: push_ll_tile<4>(t, box, slot, s_epoch); break;
@@ -354,7 +444,7 @@ __device__ __forceinline__ void halo_exchange_body(const KParams& p) {
             if (first) IGG_TRACE(3);
         } else if (LL && t.kind == kOpUnpackLL) {
             char* box = static_cast<char*>(p.field[t.field]) + t.src_off;
-            const char* slot = p.unpack_base[t.nbr] + (long long)s_half[t.nbr] * p.unpack_half + t.dst_off;
+            const char* slot = s_unpack[t.nbr] + t.dst_off;
             bool ok;
             switch (t.vec_log2) {
                 case 3: ok = unpack_ll_tile<8>(t, box, slot, s_epoch, p.timeout_ns); break;
@@ -367,7 +457,7 @@ __device__ __forceinline__ void halo_exchange_body(const KParams& p) {
         } else if (!LL && t.kind == IGG_OP_UNPACK) {
             // Wait until the neighbour has flagged this very tile (it flags each tile right after storing it).
             if (threadIdx.x == 0) {
-                const unsigned long long* flag = p.local_flags + ((long long)t.flag_idx + p.local_flag_delta[t.nbr]);
+                const unsigned long long* flag = p.local_flags + ((long long)t.flag_idx + s_lflag_delta[t.nbr]);
                 const unsigned long long want = s_epoch;
                 unsigned long long t0 = 0;
                 unsigned int spins = 0;
@@ -381,18 +471,17 @@ __device__ __forceinline__ void halo_exchange_body(const KParams& p) {
                 if (first) IGG_TRACE(5);
             }
             __syncthreads();
-            const char* src = p.unpack_base[t.nbr] + (long long)s_half[t.nbr] * p.unpack_half + t.src_off;
-            copy_tile_dispatch<true, LM>(t, src, static_cast<char*>(p.field[t.field]) + t.dst_off);
+            copy_tile_dispatch<true>(t, s_unpack[t.nbr] + t.src_off, static_cast<char*>(p.field[t.field]) + t.dst_off);
             if (first) IGG_TRACE(3);
         } else {
             // PUSH: my field -> peer staging; LOCAL: my field -> my field; COPY (gather!, NCCL pack): field -> buffer;
             // COPY_IN (NCCL unpack): buffer filled by an earlier stream operation -> my field.
-            const char* src = (t.kind == kOpCopyIn ? p.unpack_base[t.nbr] : static_cast<const char*>(p.field[t.field])) + t.src_off;
+            const char* src = (t.kind == kOpCopyIn ? p.copy_src[t.nbr] : static_cast<const char*>(p.field[t.field])) + t.src_off;
             char* dst;
             if (t.kind == IGG_OP_LOCAL || t.kind == kOpCopyIn) dst = static_cast<char*>(p.field[t.field]) + t.dst_off;
-            else if (t.kind == IGG_OP_PUSH) dst = p.push_base[t.nbr] + (long long)s_half[t.nbr] * p.push_half[t.nbr] + t.dst_off;
-            else dst = p.push_base[t.nbr] + t.dst_off;
-            copy_tile_dispatch<false, LM>(t, src, dst);
+            else if (!LL && t.kind == IGG_OP_PUSH) dst = s_push[t.nbr] + t.dst_off;
+            else dst = p.copy_dst[t.nbr] + t.dst_off;
+            copy_tile_dispatch<false>(t, src, dst);
             if (first) IGG_TRACE(3);
             if (!LL && t.kind == IGG_OP_PUSH) {
                 // Release this tile to the neighbour: all stores of the block (ordered before thread 0 by the barrier)
@@ -400,7 +489,7 @@ __device__ __forceinline__ void halo_exchange_body(const KParams& p) {
                 __syncthreads();
                 if (threadIdx.x == 0) {
                     fence_acq_rel_sys();
-                    st_relaxed_sys(p.remote_flags[t.nbr] + t.flag_idx, s_epoch);
+                    st_relaxed_sys(s_rflags[t.nbr] + t.flag_idx, s_epoch);
                     if (first) IGG_TRACE(4);
                 }
             }
@@ -412,16 +501,41 @@ __device__ __forceinline__ void halo_exchange_body(const KParams& p) {
         first = false;
         ti += gridDim.x;
         if (ti >= p.n_tiles) break;
-        t = load_tile(p.tiles + ti);
+        t = get_tile(p, ti);
     }
 
+    if (p.state && threadIdx.x == 0 && seen == gridDim.x - 1) {
+        p.state->blocks_done = 0;
+        p.state->call_epoch = s_epoch;
+        const uint32_t mask = p.plan ? p.plan->active_mask : 0u;
+        for (int o = 0; o < IGG_NOFFSETS; ++o)
+            if ((mask >> o) & 1u) p.state->exchanges[o] += 1u;
+    }
+
+    // Host-synchronous calls: the last block to finish tells the host through a mapped word (cheaper than a stream
+    // synchronisation).  Every store of the block happens-before thread 0's fence (barrier), every block's fence
+    // before its count, and the last block's system fence before the word.
+    if (p.notify) {
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            __threadfence();
+            const unsigned int fin = atomicAdd(p.fin_counter, 1u);
+            if (fin == gridDim.x - 1) {
+                *p.fin_counter = 0;
+                __threadfence_system();
+                *reinterpret_cast<volatile unsigned long long*>(p.notify) = p.notify_value;
+            }
+        }
+    }
     IGG_TRACE(6);
 #undef IGG_TRACE
 }
 
-__global__ void __launch_bounds__(kThreads, kBlocksPerSM) igg_halo_exchange_kernel(const __grid_constant__ KParams p) { halo_exchange_body<1, false>(p); }
-// The same schedule with line-formatted staging (IGG_MODE_IPC_LL128): PUSH_LL / LOCAL / UNPACK_LL tiles.
-__global__ void __launch_bounds__(kThreads, kBlocksPerSM) igg_halo_exchange_ll128_kernel(const __grid_constant__ KParams p) { halo_exchange_body<1, true>(p); }
+// Two instantiations of the one body (a single kernel with both protocols' code spills at 64 registers): plans whose
+// remote tiles are PUSH / UNPACK (fence protocol; also every plan without remote tiles, gather! and the NCCL path's
+// pack / unpack) run the first, plans with PUSH_LL / UNPACK_LL tiles (LL128) the second.
+__global__ void __launch_bounds__(kThreads, kBlocksPerSM) igg_halo_exchange_kernel(const __grid_constant__ KParams p) { halo_exchange_body<false>(p); }
+__global__ void __launch_bounds__(kThreads, kBlocksPerSM) igg_halo_exchange_ll128_kernel(const __grid_constant__ KParams p) { halo_exchange_body<true>(p); }
 }  // namespace
 
 int halo_kernel_max_coresident_blocks(int device) {
@@ -449,8 +563,7 @@ int launch_halo_kernel(const KParams& p, int grid, void* stream, bool ll128) {
     cfg.numAttrs = pdl ? 1 : 0;
     cudaError_t e = ll128 ? cudaLaunchKernelEx(&cfg, igg_halo_exchange_ll128_kernel, p)
                           : cudaLaunchKernelEx(&cfg, igg_halo_exchange_kernel, p);
-    if (e == cudaSuccess) e = cudaGetLastError();
-    if (e != cudaSuccess) return fail(IGG_ERR_CUDA, "halo kernel launch failed: %s", cudaGetErrorString(e));
+    if (e != cudaSuccess) { cudaGetLastError(); return fail(IGG_ERR_CUDA, "halo kernel launch failed: %s", cudaGetErrorString(e)); }
     return IGG_OK;
 }
 

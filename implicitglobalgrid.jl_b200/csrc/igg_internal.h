@@ -36,7 +36,8 @@ static_assert(sizeof(TileRec) == 80, "TileRec layout");
 constexpr int kThreads      = 256;      // threads per block of the halo kernel (128 measured slower: 11.6 vs 9.7 us at
                                         // 1 GPU, 22.5 vs 20.7 us at 8 GPUs on cfg2)
 constexpr int kBlocksPerSM  = 1024 / kThreads;  // launch bound: 1024 resident threads per SM at <= 64 registers
-constexpr int kTileBytes    = 8192;     // bytes moved per tile
+constexpr int kTileBytes    = 8192;     // bytes moved per LOCAL / COPY tile (bulk PUSH / UNPACK tiles: Plan::tile_bytes)
+constexpr int kMaxBulkTileBytes = 131072;
 constexpr size_t kFlagsOff   = 4096;    // control segment: arrival flags start here, one 8-byte word per tile
 constexpr int kMaxFlags      = 1 << 17; // 131 072 tiles per call (about 1 GiB of halo data)
 constexpr size_t kCtrlBytes  = kFlagsOff + (size_t)kMaxFlags * 8;
@@ -45,33 +46,68 @@ constexpr size_t kCtrlBytes  = kFlagsOff + (size_t)kMaxFlags * 8;
 struct DeviceState {
     unsigned long long call_epoch;             // exchange launches completed on this context
     unsigned int exchanges[IGG_NOFFSETS];      // exchanges completed with the neighbour at offset o (staging parity)
-    unsigned int blocks_done;                  // blocks of the running launch that have finished
+    unsigned int blocks_done;                  // blocks of the running launch that have read the state
+    unsigned int blocks_finished;              // blocks of the running launch that have finished (blocking calls only)
 };
 
-// Kernel parameters (passed by value, < 4 KB).
+// Per-plan launch constants that live in DEVICE memory (uploaded when the plan is built and again whenever the
+// context's staging layout changes): where each neighbour offset's staging and arrival flags are.  Keeping them out
+// of the kernel parameters makes a launch cheap on the host (about 350 bytes of parameters instead of 1.3 KB) and
+// keeps launches that were captured into a CUDA graph valid when the layout moves (the graph only holds the pointer).
+struct PlanDev {
+    char*       push_base[IGG_NOFFSETS];       // staging (half 0) of the peer at offset o, shifted to o's region
+    long long   push_half[IGG_NOFFSETS];       // bytes of one staging half on the peer at offset o
+    const char* unpack_base[IGG_NOFFSETS];     // my staging (half 0), shifted to offset o's region
+    unsigned long long* remote_flags[IGG_NOFFSETS];  // arrival flags in the control segment of the peer at offset o
+    int32_t     local_flag_delta[IGG_NOFFSETS];      // UNPACK tile of offset o waits for local_flags[flag_idx + delta[o]]
+    long long   unpack_half;                   // bytes of one staging half of mine
+    uint32_t    active_mask;                   // bit o: launches of this plan exchange with the neighbour at offset o
+    uint32_t    pad;
+};
+
+// One periodic x self-wrap of a field (both x-faces), as the kernel needs it to derive a kOpWrapX tile WITHOUT a
+// tile-table load: tile j of the op covers rows [j * rows_per_tile, ...) (see kOpWrapX below for the geometry).
+struct WrapXOp {
+    int64_t  src_off, dst_off, sy, sz;         // low send box, high halo box (byte offsets), row / plane strides
+    uint32_t delta;                            // (ol - hw) * elsize
+    uint32_t ny, rows, ncols, rows_per_tile;
+    uint32_t tile0;                            // first tile of this op among the launch's WRAPX tiles
+    uint16_t field;
+    uint8_t  vec_log2, pad;
+};
+constexpr int kMaxWxOps = 8;
+
+// Kernel parameters (passed by value).
 struct KParams {
     const TileRec* tiles;
     int32_t  n_tiles;
-    int32_t  n_push_tiles;                     // tiles [0, n_push_tiles) are IGG_OP_PUSH
-    void*    field[IGG_MAX_FIELDS];            // base pointers of the fields of this call
-    char*    push_base[IGG_NOFFSETS];          // staging (half 0) of the peer at offset o; COPY tiles: plain destination
-    const char* unpack_base[IGG_NOFFSETS];     // my staging (half 0); COPY_IN tiles: plain source
-    long long push_half[IGG_NOFFSETS];         // bytes of one staging half on the peer at offset o
-    long long unpack_half;                     // bytes of one staging half of mine
-    unsigned long long* remote_flags[IGG_NOFFSETS];  // arrival-flag array in the control segment of the peer at offset o
-    const unsigned long long* local_flags;     // my arrival-flag array (written by my neighbours)
-    int32_t  local_flag_delta[IGG_NOFFSETS];   // UNPACK tile of offset o waits for local_flags[flag_idx + delta[o]]
-    // Exchange state in my control segment (NULL for launches that exchange nothing: gather!, NCCL pack/unpack).
-    // It lives on the device so that the launch parameters do not change from call to call and an update_halo call
-    // can be captured into a CUDA graph and replayed: the kernel derives this call's epoch (flag value) and each
-    // neighbour's staging half from it and the last block to finish advances it.
+    int32_t  n_push_tiles;                     // tiles [0, n_push_tiles) push to a neighbour
+    const PlanDev* plan;                       // NULL for launches that exchange nothing (gather!, NCCL pack/unpack)
+    // Exchange state in my control segment (NULL for launches that exchange nothing).  It lives on the device so that
+    // the launch parameters do not change from call to call and an update_halo call can be captured into a CUDA
+    // graph and replayed: the kernel derives this call's epoch (flag value) and each neighbour's staging half from
+    // it and the last block to read it advances it.
     DeviceState* state;
-    uint32_t active_mask;                      // bit o: this launch exchanges with the neighbour at offset o
+    const unsigned long long* local_flags;     // my arrival-flag array (written by my neighbours)
     int*     status;                           // host-mapped status word (set on time-out)
     unsigned long long timeout_ns;
     unsigned long long* trace;                 // optional per-block timeline (8 words per block), NULL = off
+    // Host-synchronous calls: the last block to finish stores `notify_value` into this host-mapped word, which the
+    // host polls instead of paying a stream synchronisation (NULL = off).
+    unsigned long long* notify;
+    unsigned long long notify_value;
+    unsigned int* fin_counter;                 // blocks finished so far (device word, reset by the last block)
+    // Tiles [wx_first, wx_first + wx_count) are kOpWrapX tiles the kernel derives from `wx` below instead of loading
+    // them from the table: the strided x-face loads -- the longest latency chain of a call -- start a memory round
+    // trip earlier, and a tile-record fetch cannot queue behind the flood of strided loads (wx_count = 0: off).
+    int32_t  wx_first, wx_count, n_wx_ops;
+    WrapXOp  wx[kMaxWxOps];
+    char*       copy_dst[2];                   // kOpCopy tiles: destination buffer t.nbr (gather!, NCCL pack)
+    const char* copy_src[2];                   // kOpCopyIn tiles: source buffer t.nbr (NCCL unpack)
+    void*    field[IGG_MAX_FIELDS];            // base pointers of the fields of this call
 };
 
+constexpr int kProtoFenceDefault = 0;
 // ---- host-side plan ----------------------------------------------------------------------------------------
 struct FieldKey {
     int64_t size[3];
@@ -88,7 +124,11 @@ struct Plan {
     int                      dims_mask = 0;          // bit d set: dimension d (0..2) is updated
     std::vector<igg_plan_op> ops;                    // PUSH ops, then LOCAL, then UNPACK
     std::vector<TileRec>     tiles;
-    bool     ll128 = false;                          // tiles are kOpPushLL / LOCAL / kOpUnpackLL
+    int      proto_req = kProtoFenceDefault;         // what the caller asked for (fence, LL128 or auto)
+    bool     ll128 = false;                          // remote tiles are kOpPushLL / kOpUnpackLL (else PUSH / UNPACK)
+    int32_t  tile_bytes = kTileBytes;                // bytes per PUSH / UNPACK tile of the fence protocol (per plan)
+    int64_t  remote_bytes = 0;                       // payload bytes of all staging slots (the same on every rank)
+    bool     global_active = false;                  // some rank exchanges with another rank in this call (rank-independent)
     int32_t  n_push_tiles = 0;
     uint32_t n_flags = 0;                           // arrival flags this plan uses (must be <= kMaxFlags)
     uint32_t active_mask = 0;                        // bit o set: this plan exchanges with the neighbour at offset o
@@ -102,9 +142,14 @@ struct Plan {
     int64_t  region_pack[IGG_NOFFSETS] = {0}, region_need[IGG_NOFFSETS] = {0};
     uint32_t flag_pack[IGG_NOFFSETS] = {0}, flag_need[IGG_NOFFSETS] = {0};
     int64_t  bytes_sent = 0;                         // algorithmic halo bytes this rank sends (local + remote)
-    // device copy (owned by the context)
+    // device copy (owned by the context): [PlanDev | tiles] in one allocation
+    PlanDev* d_plan = nullptr;
     TileRec* d_tiles = nullptr;
     int      grid = 0;
+    bool     pinned = false;                         // referenced by a prepared call or a stream capture: never evicted
+    // kOpWrapX tiles: where they are in `tiles` and the per-op descriptors they were cut from
+    int32_t  wx_first = 0, wx_count = 0;
+    std::vector<WrapXOp>     wx_ops;
     // kOpWrapLines tiles of host-resident fields (run by igg_wrap_lines_kernel, one block each)
     std::vector<TileRec>     wrap_tiles;
     TileRec* d_wrap_tiles = nullptr;
@@ -124,9 +169,14 @@ int check_fields(const igg_grid_desc& g, int nfields, const igg_field* fields);
 int ranges(const igg_grid_desc& g, const igg_field& f, int n, int dim, bool send, int64_t out[6]);
 // Builds ops + tiles for this rank.  Pure host code.  `host_lines[i]` != 0 (optional): field i lives in page-locked
 // host memory on a 64-byte boundary, so its periodic x self-wrap may be emitted as kOpWrapLines tiles.
-// `ll128`: emit PUSH / UNPACK as kOpPushLL / kOpUnpackLL tiles over line-formatted staging (IGG_MODE_IPC_LL128).
+// `proto`: how data that goes to another rank is staged -- kProtoFence: PUSH / UNPACK tiles, one release fence and
+// arrival flag per tile (tile size grows with the call: the bandwidth regime); kProtoLL128: kOpPushLL / kOpUnpackLL
+// tiles over line-formatted staging (the latency regime); kProtoAuto: LL128 below auto_bulk_threshold() payload bytes
+// per call, the fence protocol above (decided from numbers that are the same on every rank).
+constexpr int kProtoFence = 0, kProtoLL128 = 1, kProtoAuto = 2;
+int64_t auto_bulk_threshold();
 int build_plan(const igg_grid_desc& g, int nfields, const igg_field* fields, int dims_mask, Plan& plan,
-               const uint8_t* host_lines = nullptr, bool ll128 = false);
+               const uint8_t* host_lines = nullptr, int proto = kProtoFence);
 void build_block_copy_tiles(int64_t el, const int64_t ext[3], const int64_t dst_size[2], const int64_t dst_origin[3],
                             int64_t src_align, int64_t dst_align, std::vector<TileRec>& tiles);
 constexpr int kOpCopy = 3;   // internal tile kind: field[t.field] -> push_base[t.nbr], no signalling (gather!, NCCL pack)
@@ -150,6 +200,16 @@ constexpr int kWrapRowsPerTile = 128;
 // staging half, dst_sy = payload bytes of the slot; vec_log2 = log2(W); nbr as for PUSH / UNPACK.
 constexpr int kOpPushLL = 6;
 constexpr int kOpUnpackLL = 7;
+// Periodic x self-wrap of device-resident fields, one thread per (row, word): the thread loads the row's low send
+// word and its high send word together and stores them into the high halo and the low halo.  Replaces the two LOCAL
+// ops (-x and +x) of a field, which walked the same rows twice; a send cell and the halo cell beside it share a
+// 32-byte sector, so the row's two sectors are fetched once (profiles/xface_floor.cu: 6.8 us vs 9.2 us per 256^3 f64
+// x-wrap, cold L2).
+// TileRec use: src_off = byte offset of the low send box, dst_off = of the high halo box (row 0 of the tile's box),
+// src_sy / src_sz = row / plane strides, dst_sy = (ol - hw) * elsize (high send = high halo - dst_sy, low halo =
+// low send - dst_sy), ncols = words per side per row, row0 / nrows / ny as for copy tiles.
+constexpr int kOpWrapX = 8;
+constexpr int kWrapXRowsPerTile = 256;
 constexpr int kLinePayload = 120;
 constexpr int kLinesPerTile = 64;
 int build_dim_phase(const igg_grid_desc& g, int nfields, const igg_field* fields, int d, std::vector<TileRec>& pack,

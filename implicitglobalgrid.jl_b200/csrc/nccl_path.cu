@@ -179,7 +179,7 @@ int nccl_phase(NcclPath* np, const igg_grid_desc& g, int nfields, const igg_fiel
     KParams p = proto;
     for (int i = 0; i < nfields; ++i) p.field[i] = fields[i].ptr;
     p.n_push_tiles = 0;
-    for (int n = 0; n < 2; ++n) { p.push_base[n] = np->sendbuf[n]; p.unpack_base[n] = np->recvbuf[n]; }
+    for (int n = 0; n < 2; ++n) { p.copy_dst[n] = np->sendbuf[n]; p.copy_src[n] = np->recvbuf[n]; }
     // pack (replaces iwrite_sendbufs!, ref: src/CUDAExt/update_halo.jl:161-174)
     p.tiles = e->d_pack;
     p.n_tiles = e->n_pack;

@@ -14,6 +14,7 @@
 #include <algorithm>
 #include <array>
 #include <cstdarg>
+#include <cstdlib>
 
 #include "igg_internal.h"
 
@@ -178,7 +179,7 @@ struct Lowered { int64_t src_off, dst_off, s_sy, s_sz, d_sy, d_sz, row, ny, nz, 
 
 Lowered emit_tiles(int64_t el, const int64_t ext[3], int64_t src_off, int64_t s_sy, int64_t s_sz, int64_t dst_off,
                    int64_t d_sy, int64_t d_sz, int64_t src_align, int64_t dst_align, int field_idx, int kind, int nbr,
-                   std::vector<TileRec>& tiles) {
+                   std::vector<TileRec>& tiles, int64_t tile_bytes = kTileBytes) {
     int64_t row = ext[0] * el, ny = ext[1], nz = ext[2];
     if (ny == 1) { ny = nz; nz = 1; s_sy = s_sz; d_sy = d_sz; }
     while (ny > 1 && s_sy == row && d_sy == row) { row *= ny; ny = nz; nz = 1; s_sy = s_sz; d_sy = d_sz; }
@@ -197,7 +198,7 @@ Lowered emit_tiles(int64_t el, const int64_t ext[3], int64_t src_off, int64_t s_
     while ((1 << vlog) < v) ++vlog;
 
     const int64_t V = row / v, rows = ny * nz;
-    const int64_t per_tile = kTileBytes / v;
+    const int64_t per_tile = tile_bytes / v;
     int64_t S, R;
     if (V >= per_tile) { S = per_tile; R = 1; } else { S = V; R = std::max<int64_t>(1, per_tile / V); }
     const int64_t segs = (V + S - 1) / S, rblocks = (rows + R - 1) / R;
@@ -224,7 +225,8 @@ Lowered emit_tiles(int64_t el, const int64_t ext[3], int64_t src_off, int64_t s_
 // Fills the merged low-level form + tiles of one op.  `src_field` / `dst_field`: the box lives in the field array
 // (strides of the field) or in a packed staging slot (strides of the box itself, origin = staging_off).
 void lower_op(const igg_field& f, int field_idx, int kind, int nbr, const Box& sb, const Box& db, bool src_field,
-              bool dst_field, int64_t staging_off, igg_plan_op& op, std::vector<TileRec>& tiles) {
+              bool dst_field, int64_t staging_off, igg_plan_op& op, std::vector<TileRec>& tiles,
+              int64_t tile_bytes = kTileBytes) {
     const int64_t el = f.elsize;
     int64_t b[3];
     for (int d = 0; d < 3; ++d) b[d] = sb.hi[d] - sb.lo[d] + 1;
@@ -235,7 +237,7 @@ void lower_op(const igg_field& f, int field_idx, int kind, int nbr, const Box& s
     const Lowered L = emit_tiles(el, b, src_field ? field_off(sb) : staging_off, src_field ? fsy : psy,
                                  src_field ? fsz : psz, dst_field ? field_off(db) : staging_off, dst_field ? fsy : psy,
                                  dst_field ? fsz : psz, src_field ? align : 0, dst_field ? align : 0, field_idx, kind,
-                                 nbr, tiles);
+                                 nbr, tiles, tile_bytes);
     op.src_off = L.src_off; op.dst_off = L.dst_off;
     op.src_sy = L.s_sy; op.src_sz = L.s_sz; op.dst_sy = L.d_sy; op.dst_sz = L.d_sz;
     op.row_bytes = L.row; op.ny = L.ny; op.nz = L.nz;
@@ -246,9 +248,18 @@ void lower_op(const igg_field& f, int field_idx, int kind, int nbr, const Box& s
 
 }  // namespace
 
+// Payload bytes per call above which kProtoAuto stages through the fence protocol (16-byte accesses, big tiles)
+// instead of LL128 lines.  IGG_BULK_THRESHOLD (bytes) overrides it; it must be the same on every rank.
+int64_t auto_bulk_threshold() {
+    static const int64_t v = [] {
+        const char* e = getenv("IGG_BULK_THRESHOLD");
+        return (e && *e) ? (int64_t)atoll(e) : (int64_t)8 << 20;
+    }();
+    return v;
+}
+
 int build_plan(const igg_grid_desc& g, int nfields, const igg_field* fields, int dims_mask, Plan& plan,
-               const uint8_t* host_lines, bool ll128) {
-    plan.ll128 = ll128;
+               const uint8_t* host_lines, int proto) {
     int rc = check_grid(g);
     if (rc) return rc;
     rc = check_fields(g, nfields, fields);
@@ -268,6 +279,7 @@ int build_plan(const igg_grid_desc& g, int nfields, const igg_field* fields, int
     plan.ops.clear();
     plan.tiles.clear();
     plan.wrap_tiles.clear();
+    plan.wx_ops.clear();
     plan.active_mask = 0;
     plan.bytes_sent = 0;
 
@@ -282,19 +294,41 @@ int build_plan(const igg_grid_desc& g, int nfields, const igg_field* fields, int
             halo[i][d] = ((dims_mask >> d) & 1) && field_ol(g, fields[i], d) >= 2 * fields[i].halowidths[d] &&
                          (g.dims[d] > 1 || g.periods[d]);   // no rank has a neighbour in d otherwise (global fact)
 
-    // Every rank must take part in a call or none (the exchange epoch is compared across ranks).  An array without
-    // interior cells in an exchanged dimension could leave interior ranks with nothing to copy: refuse it loudly.
+    // Every rank must take part in a call or none (the exchange epoch is compared across ranks): whether a call
+    // exchanges between ranks at all is decided from numbers that are the same everywhere.  A rank that happens to
+    // have nothing to copy (arrays without interior cells, ref: src/update_halo.jl:239 accepts them) still launches.
+    plan.global_active = false;
     for (int i = 0; i < nfields; ++i)
-        for (int d = 0; d < 3; ++d)
-            if (halo[i][d] && g.nprocs > 1 && fields[i].size[d] <= 2 * fields[i].halowidths[d])
-                return fail(IGG_ERR_UNSUPPORTED,
-                            "The field at position %d has no interior cells in dimension %d (size %lld <= 2*halowidth %lld); "
-                            "such arrays are not supported on more than one rank.", i + 1, d + 1,
-                            (long long)fields[i].size[d], (long long)(2 * fields[i].halowidths[d]));
+        for (int d = 0; d < 3; ++d) plan.global_active = plan.global_active || (halo[i][d] && g.dims[d] > 1);
 
     // Staging slots: one per (offset, field), identical on every rank (depends only on field sizes, halowidths and
     // the updated dimensions, never on which neighbours exist), so a sender can compute the receiver's layout.
     std::vector<int64_t> slot_off((size_t)IGG_NOFFSETS * nfields, -1);
+    std::vector<int64_t> slot_n((size_t)IGG_NOFFSETS * nfields, 0);
+    plan.remote_bytes = 0;
+    for (int oi = 0; oi < IGG_NOFFSETS; ++oi) {
+        int o[3];
+        index_offset(oi, o);
+        if (!o[0] && !o[1] && !o[2]) continue;
+        for (int i = 0; i < nfields; ++i) {
+            bool ok = true, remote = false;     // remote: the rank at this offset is another rank (on every rank alike)
+            int64_t n = fields[i].elsize;
+            for (int d = 0; d < 3; ++d) {
+                if (o[d]) { ok = ok && halo[i][d]; remote = remote || g.dims[d] > 1; n *= fields[i].halowidths[d]; }
+                else n *= fields[i].size[d];
+            }
+            if (!ok || !remote) continue;       // self-wraps copy inside the array and need no staging slot
+            slot_n[(size_t)oi * nfields + i] = n;
+            plan.remote_bytes += n;
+        }
+    }
+    const bool ll128 = proto == kProtoLL128 || (proto == kProtoAuto && plan.remote_bytes < auto_bulk_threshold());
+    plan.ll128 = ll128;
+    // Fence protocol: tiles grow with the call so that a call has a few hundred PUSH tiles (one release fence each),
+    // whatever its size: 8 KiB ... 128 KiB, the same number on every rank.
+    int64_t tb = kTileBytes;
+    while (tb < kMaxBulkTileBytes && plan.remote_bytes / tb > 256) tb *= 2;
+    plan.tile_bytes = (int32_t)tb;
     // Arrival flags: one per tile.  A slot reserves an upper bound of the tiles any box that fits it can have
     // (every full tile covers more than kTileBytes/2 bytes), so that flag numbers too are identical on every rank.
     std::vector<uint32_t> slot_flag((size_t)IGG_NOFFSETS * nfields, 0), slot_nflag((size_t)IGG_NOFFSETS * nfields, 0);
@@ -315,21 +349,18 @@ int build_plan(const igg_grid_desc& g, int nfields, const igg_field* fields, int
         if (!o[0] && !o[1] && !o[2]) continue;
         plan.peer[oi] = -1;
         for (int i = 0; i < nfields; ++i) {
-            bool ok = true, remote = false;     // remote: the rank at this offset is another rank (on every rank alike)
-            int64_t n = fields[i].elsize;
-            for (int d = 0; d < 3; ++d) {
-                if (o[d]) { ok = ok && halo[i][d]; remote = remote || g.dims[d] > 1; n *= fields[i].halowidths[d]; }
-                else n *= fields[i].size[d];
-            }
-            if (!ok || !remote) continue;       // self-wraps copy inside the array and need no staging slot
+            const int64_t n = slot_n[(size_t)oi * nfields + i];
+            if (n == 0) continue;
             slot_off[(size_t)oi * nfields + i] = total;
             if (ll128) {                        // lines of 120 payload bytes + 8 flag bytes; no separate flags
+                if (n >= (int64_t)1 << 32)
+                    return fail(IGG_ERR_ARG, "update_halo: a halo box of 4 GiB or more is not supported by the LL128 protocol.");
                 total += (n + kLinePayload - 1) / kLinePayload * 128;
                 continue;
             }
             total += round_up(n, 128);
             slot_flag[(size_t)oi * nfields + i] = nflags;
-            slot_nflag[(size_t)oi * nfields + i] = (uint32_t)(2 * ((n + kTileBytes - 1) / kTileBytes) + 1);
+            slot_nflag[(size_t)oi * nfields + i] = (uint32_t)(2 * ((n + tb - 1) / tb) + 1);
             nflags += slot_nflag[(size_t)oi * nfields + i];
         }
     }
@@ -338,7 +369,7 @@ int build_plan(const igg_grid_desc& g, int nfields, const igg_field* fields, int
     plan.n_flags = nflags;
 
     std::vector<igg_plan_op> push, local, unpack;
-    std::vector<TileRec> tpush, tlocal, tunpack;
+    std::vector<TileRec> tpush, twrapx, tlocal, tunpack;
 
     for (int oi = 0; oi < IGG_NOFFSETS; ++oi) {
         int o[3];
@@ -428,6 +459,41 @@ int build_plan(const igg_grid_desc& g, int nfields, const igg_field* fields, int
                             plan.wrap_tiles.push_back(t);
                         }
                     }
+                } else if (o[0] && !o[1] && !o[2] && exists[0][0] && exists[0][1]) {
+                    // The two x-faces of a device-resident field wrap together (kOpWrapX): the -x op emits the tiles
+                    // for both sides, one thread per row and word doing both directions.  The op descriptions stay
+                    // the cell-level ones.  (The -x and +x boxes cover the same rows.)
+                    std::vector<TileRec> unused;
+                    lower_op(f, i, IGG_OP_LOCAL, oi, snd, rcv_peer, true, true, 0, op, unused);
+                    if (o[0] < 0) {
+                        const int64_t hwb = f.halowidths[0] * el, delta = (field_ol(g, f, 0) - f.halowidths[0]) * el;
+                        const int64_t fsy = pitch, fsz = pitch * f.size[1];
+                        const int64_t ny = snd.hi[1] - snd.lo[1] + 1, nz = snd.hi[2] - snd.lo[2] + 1, rows = ny * nz;
+                        const int64_t row_org = (snd.lo[1] - 1) * fsy + (snd.lo[2] - 1) * fsz;
+                        const int64_t lo_send = row_org + delta, hi_halo = row_org + (f.size[0] - f.halowidths[0]) * el;
+                        const int64_t align = (int64_t)((uintptr_t)f.ptr % 16);
+                        int64_t v = 16;
+                        while (v > 1 && (hwb % v || delta % v || (align + lo_send) % v || (align + hi_halo) % v || fsy % v || fsz % v)) v /= 2;
+                        int vlog = 0;
+                        while ((1 << vlog) < v) ++vlog;
+                        const int64_t ncols = hwb / v, per = std::max<int64_t>(1, kWrapXRowsPerTile / ncols);
+                        WrapXOp w;
+                        std::memset(&w, 0, sizeof(w));
+                        w.src_off = lo_send; w.dst_off = hi_halo; w.sy = fsy; w.sz = fsz; w.delta = (uint32_t)delta;
+                        w.ny = (uint32_t)ny; w.rows = (uint32_t)rows; w.ncols = (uint32_t)ncols; w.rows_per_tile = (uint32_t)per;
+                        w.tile0 = (uint32_t)twrapx.size(); w.field = (uint16_t)i; w.vec_log2 = (uint8_t)vlog;
+                        plan.wx_ops.push_back(w);
+                        for (int64_t r0 = 0; r0 < rows; r0 += per) {
+                            TileRec t;
+                            std::memset(&t, 0, sizeof(t));
+                            t.src_off = lo_send; t.dst_off = hi_halo;
+                            t.src_sy = fsy; t.src_sz = fsz; t.dst_sy = delta;
+                            t.row0 = (uint32_t)r0; t.nrows = (uint32_t)std::min<int64_t>(per, rows - r0);
+                            t.ncols = (uint32_t)ncols; t.ny = (uint32_t)ny;
+                            t.field = (uint16_t)i; t.vec_log2 = (uint8_t)vlog; t.kind = (uint8_t)kOpWrapX; t.nbr = (uint8_t)oi;
+                            twrapx.push_back(t);
+                        }
+                    }
                 } else {
                     lower_op(f, i, IGG_OP_LOCAL, oi, snd, rcv_peer, true, true, 0, op, tlocal);
                 }
@@ -456,8 +522,6 @@ int build_plan(const igg_grid_desc& g, int nfields, const igg_field* fields, int
                     };
                     std::vector<TileRec> unused;
                     lower_op(f, i, IGG_OP_PUSH, oi, snd, snd, true, false, op.staging_off, op, unused);
-                    if (op.row_bytes >= (int64_t)1 << 32)
-                        return fail(IGG_ERR_ARG, "update_halo: a contiguous run of 4 GiB or more is not supported in LL128 mode.");
                     op.flag_base = -1;
                     emit_ll(kOpPushLL, op.src_off, op.src_sy, op.src_sz, op, tpush);
                     push.push_back(op);
@@ -482,7 +546,7 @@ int build_plan(const igg_grid_desc& g, int nfields, const igg_field* fields, int
                     continue;
                 }
                 const size_t first_push = tpush.size();
-                lower_op(f, i, IGG_OP_PUSH, oi, snd, snd, true, false, op.staging_off, op, tpush);
+                lower_op(f, i, IGG_OP_PUSH, oi, snd, snd, true, false, op.staging_off, op, tpush, tb);
                 if (tpush.size() - first_push > slot_nflag[(size_t)opposite_index(oi) * nfields + i])
                     return fail(IGG_ERR_STATE, "internal: an exchange op has more tiles than its slot has arrival flags.");
                 for (size_t k = first_push; k < tpush.size(); ++k)      // flag numbers in the RECEIVER's slot table
@@ -504,7 +568,7 @@ int build_plan(const igg_grid_desc& g, int nfields, const igg_field* fields, int
                 }
                 up.staging_off = slot_off[(size_t)oi * nfields + i];
                 const size_t first_unpack = tunpack.size();
-                lower_op(f, i, IGG_OP_UNPACK, oi, rcv_mine, rcv_mine, false, true, up.staging_off, up, tunpack);
+                lower_op(f, i, IGG_OP_UNPACK, oi, rcv_mine, rcv_mine, false, true, up.staging_off, up, tunpack, tb);
                 for (size_t k = first_unpack; k < tunpack.size(); ++k)
                     tunpack[k].flag_idx = slot_flag[(size_t)oi * nfields + i] + (uint32_t)(k - first_unpack);
                 up.flag_base = (int32_t)slot_flag[(size_t)oi * nfields + i];
@@ -517,8 +581,14 @@ int build_plan(const igg_grid_desc& g, int nfields, const igg_field* fields, int
     plan.ops = push;
     plan.ops.insert(plan.ops.end(), local.begin(), local.end());
     plan.ops.insert(plan.ops.end(), unpack.begin(), unpack.end());
+    // Order: PUSH, LOCAL, WRAPX, UNPACK.  Blocks are dispatched in index order, so the contiguous copies have their
+    // tile records and their loads out before the strided x-face loads flood the memory system (measured: with WRAPX
+    // first a few LOCAL blocks got their tile record 3-4.6 us late and ended the launch at 9.7 us instead of 7.5).
     plan.tiles = tpush;
     plan.tiles.insert(plan.tiles.end(), tlocal.begin(), tlocal.end());
+    plan.wx_first = (int32_t)plan.tiles.size();
+    plan.wx_count = (int32_t)twrapx.size();
+    plan.tiles.insert(plan.tiles.end(), twrapx.begin(), twrapx.end());
     plan.tiles.insert(plan.tiles.end(), tunpack.begin(), tunpack.end());
     return IGG_OK;
 }
@@ -624,12 +694,14 @@ int igg_plan_tiles(const igg_grid_desc* desc, int nfields, const igg_field* fiel
                    int mode, void* tiles_out, int tiles_cap, int* ntiles_out, int64_t* staging_bytes_out,
                    int64_t* regions_out) {
     if (!desc || !fields || !ntiles_out) return igg::fail(IGG_ERR_ARG, "igg_plan_tiles: NULL argument.");
-    if (mode != IGG_MODE_IPC_1PHASE && mode != IGG_MODE_IPC_LL128) return igg::fail(IGG_ERR_ARG, "igg_plan_tiles: mode must be an IPC mode.");
+    if (mode != IGG_MODE_IPC_1PHASE && mode != IGG_MODE_IPC_LL128 && mode != IGG_MODE_IPC_AUTO)
+        return igg::fail(IGG_ERR_ARG, "igg_plan_tiles: mode must be an IPC mode.");
     int mask;
     int rc = igg::dims_mask_from_order(dims_order, ndims_order, &mask);
     if (rc) return rc;
     igg::Plan plan;
-    rc = igg::build_plan(*desc, nfields, fields, mask, plan, nullptr, mode == IGG_MODE_IPC_LL128);
+    rc = igg::build_plan(*desc, nfields, fields, mask, plan, nullptr,
+                         mode == IGG_MODE_IPC_LL128 ? igg::kProtoLL128 : mode == IGG_MODE_IPC_AUTO ? igg::kProtoAuto : igg::kProtoFence);
     if (rc) return rc;
     *ntiles_out = (int)plan.tiles.size();
     if (staging_bytes_out) *staging_bytes_out = plan.staging_bytes;

@@ -15,7 +15,7 @@ IGG_OK = 0
 IGG_ERR_ARG, IGG_ERR_CUDA, IGG_ERR_STATE, IGG_ERR_FIELDS, IGG_ERR_IPC = -1, -2, -3, -4, -5
 IGG_ERR_NCCL, IGG_ERR_TIMEOUT, IGG_ERR_UNSUPPORTED, IGG_ERR_GRID = -6, -7, -8, -9
 IGG_SYNC, IGG_ASYNC = 0, 1
-IGG_MODE_IPC_1PHASE, IGG_MODE_NCCL_3PHASE, IGG_MODE_IPC_LL128 = 0, 1, 2
+IGG_MODE_IPC_1PHASE, IGG_MODE_NCCL_3PHASE, IGG_MODE_IPC_LL128, IGG_MODE_IPC_AUTO = 0, 1, 2, 3
 IGG_NOFFSETS = 27
 IGG_OP_PUSH, IGG_OP_LOCAL, IGG_OP_UNPACK = 0, 1, 2
 IGG_PROC_NULL = -1
@@ -78,6 +78,9 @@ def load():
         "igg_bootstrap_export": (C.c_int, [vp, vp]),
         "igg_bootstrap_import": (C.c_int, [vp, vp, i32]),
         "igg_update_halo": (C.c_int, [vp, i32, fp, i32p, i32, vp, i32]),
+        "igg_prepare": (C.c_int, [vp, i32, fp, i32p, i32, C.POINTER(vp)]),
+        "igg_update_halo_prepared": (C.c_int, [vp, vp, i32]),
+        "igg_release_prepared": (C.c_int, [vp]),
         "igg_update_halo_noalloc": (C.c_int, [gd, i32, fp, i32p, i32, vp, i32]),
         "igg_noalloc_scratch_bytes": (C.c_int64, []),
         "igg_set_mode": (C.c_int, [vp, i32]),
@@ -95,6 +98,8 @@ def load():
         "igg_ctrl_selftest_create": (C.c_int, [i32, i32, C.c_char_p, C.POINTER(vp)]),
         "igg_ctrl_selftest_run": (C.c_int, [vp, i32, i32, C.c_char_p, i32]),
         "igg_debug_state": (C.c_int, [vp, C.POINTER(C.c_uint64)]),
+        "igg_debug_issue_loop": (C.c_int, [vp, vp, i32, C.POINTER(C.c_double)]),
+        "igg_debug_timed_calls": (C.c_int, [C.POINTER(vp), i32, vp, i32, i32, C.POINTER(C.c_float), C.POINTER(C.c_double)]),
         "igg_trace_enable": (C.c_int, [vp, i32]),
         "igg_trace_read": (C.c_int, [vp, C.POINTER(C.c_uint64), i32, i32p]),
         "igg_launch_count": (C.c_int64, [vp]),
@@ -110,9 +115,9 @@ def load():
 
 DECLARED_SYMBOLS = [
     "igg_version", "igg_last_error", "igg_create", "igg_destroy", "igg_bootstrap_size", "igg_bootstrap_export",
-    "igg_bootstrap_import", "igg_update_halo", "igg_update_halo_noalloc", "igg_noalloc_scratch_bytes", "igg_set_mode", "igg_nccl_unique_id_size", "igg_nccl_get_unique_id",
+    "igg_bootstrap_import", "igg_update_halo", "igg_prepare", "igg_update_halo_prepared", "igg_release_prepared", "igg_update_halo_noalloc", "igg_noalloc_scratch_bytes", "igg_set_mode", "igg_nccl_unique_id_size", "igg_nccl_get_unique_id",
     "igg_nccl_init", "igg_gather", "igg_diffusion3d_step", "igg_sendranges", "igg_recvranges", "igg_check_fields", "igg_plan_describe", "igg_plan_tiles",
-    "igg_ctrl_selftest_create", "igg_ctrl_selftest_run", "igg_debug_state", "igg_trace_enable", "igg_trace_read",
+    "igg_ctrl_selftest_create", "igg_ctrl_selftest_run", "igg_debug_state", "igg_debug_issue_loop", "igg_debug_timed_calls", "igg_trace_enable", "igg_trace_read",
     "igg_launch_count", "igg_kernel_name",
 ]
 

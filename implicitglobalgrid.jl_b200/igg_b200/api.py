@@ -352,20 +352,24 @@ def update_halo(*A, dims=(3, 1, 2), stream=None, blocking=True):
 
 
 def set_exchange_mode(mode):
-    """Selects how update_halo moves data between ranks.  "ipc": the default (one fused kernel, peer stores over
-    NVLink, protocol "ll128" unless the environment says IGG_MODE=fence).  "ll128": every 128-byte line of staged data
-    carries its own arrival flag, so there is no release fence and no separate flag.  "fence": one release fence and
-    one arrival flag per 8-KiB tile.  "nccl": comparison path (per-dimension pack kernel, grouped ncclSend/ncclRecv,
-    unpack kernel).  Collective."""
+    """Selects how update_halo moves data between ranks.  "ipc": the mode new contexts start in (one fused kernel, peer
+    stores over NVLink; "auto" unless the environment variable IGG_MODE names another).  "auto": per call, "ll128"
+    below IGG_BULK_THRESHOLD staged bytes (default 8 MiB), "fence" above.  "ll128": every 128-byte line of staged data
+    carries its own arrival flag, so there is no release fence and no separate flag (latency regime).  "fence":
+    16-byte accesses, one release fence and one arrival flag per tile of 8-128 KiB (bandwidth regime).  "nccl":
+    comparison path (per-dimension pack kernel, grouped ncclSend/ncclRecv, unpack kernel).  Every rank must select
+    the same mode."""
     g = global_grid()
     lib = L.load()
-    if mode == "ipc":        # the protocol new contexts start in: LL128 unless the environment says IGG_MODE=fence
-        mode = "fence" if os.environ.get("IGG_MODE") in ("fence", "ipc") else "ll128"
-    if mode in ("fence", "ll128"):
-        L.check(lib.igg_set_mode(g.ctx, L.IGG_MODE_IPC_1PHASE if mode == "fence" else L.IGG_MODE_IPC_LL128))
+    if mode == "ipc":
+        env = os.environ.get("IGG_MODE")
+        mode = "fence" if env in ("fence", "ipc") else env if env in ("ll128", "auto") else "auto"
+    if mode in ("fence", "ll128", "auto"):
+        L.check(lib.igg_set_mode(g.ctx, {"fence": L.IGG_MODE_IPC_1PHASE, "ll128": L.IGG_MODE_IPC_LL128,
+                                         "auto": L.IGG_MODE_IPC_AUTO}[mode]))
         return
     if mode != "nccl":
-        raise ArgumentError(f"unknown exchange mode {mode!r} (use 'ipc', 'fence', 'll128' or 'nccl')")
+        raise ArgumentError(f"unknown exchange mode {mode!r} (use 'ipc', 'auto', 'fence', 'll128' or 'nccl')")
     if g.nprocs > 1:
         n = lib.igg_nccl_unique_id_size()
         buf = C.create_string_buffer(n)
@@ -377,26 +381,61 @@ def set_exchange_mode(mode):
     L.check(lib.igg_set_mode(g.ctx, L.IGG_MODE_NCCL_3PHASE))
 
 
-def prepare_update_halo(*A, dims=(3, 1, 2), stream=None, blocking=True):
-    """Validates the arguments once and returns a zero-argument callable that performs `update_halo!(A...)` with
-    minimal host overhead (one foreign call).  For time loops that update the same arrays every step.  The arrays
-    must stay alive and in place; `stream` defaults to the stream current at preparation time."""
-    A = _extract_all(A)
-    update_halo(*A, dims=dims, stream=stream, blocking=True)      # validates, builds the plan, warms the caches
-    key = (tuple(_field_key(a) for a in A), tuple(dims))
-    arr, nf, d, nd = _call_cache[key]
-    lib = L.load()
-    fn = lib.igg_update_halo
-    ctx = _grid.ctx
-    s = stream.cuda_stream if stream is not None else _torch().cuda.current_stream().cuda_stream
-    flags = L.IGG_SYNC if blocking else L.IGG_ASYNC
-    keep = (A, arr, d)                                            # keep the ctypes buffers and tensors alive
+class PreparedCall:
+    """A validated `update_halo!(A...)` kept for reuse (igg_prepare): calling it performs the update through one
+    foreign call that skips argument checks, pointer resolution and plan lookup."""
 
-    def call():
-        rc = fn(ctx, nf, arr, d, nd, s, flags)
+    def __init__(self, A, dims, stream, blocking):
+        g = global_grid()
+        lib = L.load()
+        A = _extract_all(A)
+        fields = [_wrap(a) for a in A]
+        diff = [i + 1 for i in range(1, len(fields))
+                if fields[i][0].dtype != fields[0][0].dtype or fields[i][0].dim() != fields[0][0].dim()]
+        if diff:
+            raise ArgumentError(f"The field at position {diff[0]} is of different type than the first field; make sure "
+                                "that in a same call all fields are of the same type.")
+        cf = _c_fields(fields)
+        arr = (L.Field * len(cf))(*cf)
+        d = (C.c_int * len(dims))(*[int(x) for x in dims])
+        h = C.c_void_p()
+        L.check(lib.igg_prepare(g.ctx, len(cf), arr, d, len(dims), C.byref(h)))
+        self._h, self._lib, self._fn = h, lib, lib.igg_update_halo_prepared
+        self._keep = (A, arr, d)                                  # the tensors must stay alive and in place
+        self._s = C.c_void_p(stream.cuda_stream if stream is not None else _torch().cuda.current_stream().cuda_stream)
+        self._flags = L.IGG_SYNC if blocking else L.IGG_ASYNC
+        self._ctx = g.ctx
+        import functools
+        self._go = functools.partial(self._fn, self._h, self._s, self._flags)      # one foreign call, arguments prebuilt
+
+    def __call__(self):
+        if self._go():
+            L.check(self._fn(self._h, self._s, self._flags) or 0)
+
+    def release(self):
+        if self._h is not None:
+            self._lib.igg_release_prepared(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.release()
+        except Exception:
+            pass
+
+
+def prepare_update_halo(*A, dims=(3, 1, 2), stream=None, blocking=True, warm=True):
+    """Validates the arguments once and returns a zero-argument callable that performs `update_halo!(A...)` with
+    minimal host overhead (igg_prepare / igg_update_halo_prepared).  For time loops that update the same arrays every
+    step.  The arrays must stay alive and in place; `stream` defaults to the stream current at preparation time.
+    With `warm` (default) one host-synchronous update is performed right away, like a first `update_halo!` call: it
+    is collective, and it makes the context grow its staging memory now rather than inside the time loop or a CUDA
+    graph capture (updating twice gives the same halos as updating once).  `warm=False` only prepares."""
+    call = PreparedCall(A, dims, stream, blocking)
+    if warm:
+        rc = call._fn(call._h, call._s, L.IGG_SYNC)
         if rc:
             L.check(rc)
-        return keep and None
     return call
 
 

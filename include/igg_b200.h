@@ -48,17 +48,20 @@ enum igg_flags {
 };
 
 enum igg_mode {
-    IGG_MODE_IPC_1PHASE = 0,  /* one fused kernel, all 26 neighbour regions in one phase, peer stores over NVLink, one
-                                 release fence + arrival flag per 8-KiB tile ("fence" protocol; env IGG_MODE=fence
-                                 makes new contexts start in it) */
+    IGG_MODE_IPC_1PHASE = 0,  /* one fused kernel, all 26 neighbour regions in one phase, peer stores over NVLink with
+                                 16-byte accesses, one release fence + arrival flag per tile of 8-128 KiB ("fence"
+                                 protocol, the bandwidth regime; env IGG_MODE=fence makes new contexts start in it) */
     IGG_MODE_NCCL_3PHASE = 1, /* comparison path: pack kernel -> grouped ncclSend/ncclRecv -> unpack kernel, one
                                  phase per dimension in the reference's order (ref: src/update_halo.jl:51-88) */
-    IGG_MODE_IPC_LL128 = 2    /* DEFAULT.  Like IGG_MODE_IPC_1PHASE, but the staged data carries its own arrival flags: every
+    IGG_MODE_IPC_LL128 = 2,   /* Like IGG_MODE_IPC_1PHASE, but the staged data carries its own arrival flags: every
                                  128-byte line of staging is 120 bytes of payload + the call's 8-byte epoch, stored by
                                  one warp instruction, so the sender needs neither a release fence nor a separate flag
-                                 and the receiver unpacks each line as it lands.  Selecting it (or leaving it) is
-                                 collective: all ranks call igg_set_mode together; it clears the staging memory. */
+                                 and the receiver unpacks each line as it lands (the latency regime; IGG_MODE=ll128). */
+    IGG_MODE_IPC_AUTO = 3     /* DEFAULT.  Per call: LL128 when the call stages less than IGG_BULK_THRESHOLD bytes per
+                                 rank (default 8 MiB), the fence protocol above.  The choice is made from the field
+                                 sizes, so every rank makes the same one.  Each protocol has staging of its own. */
 };
+/* igg_set_mode is collective in the sense that every rank must select the same mode before the next update. */
 
 /* Mirror of the reference's GlobalGrid (ref: src/shared.jl:58-81), reduced to what the halo path reads.
  * `neighbors[d][s]` is the rank of the neighbour in dimension d (0..2) on side s (0 = left/low, 1 = right/high)
@@ -125,6 +128,20 @@ int    igg_bootstrap_import(igg_ctx* ctx, const void* all_blobs, int nprocs);
  * `stream` is a cudaStream_t (NULL = default stream); the call is ordered after prior work on it. */
 int igg_update_halo(igg_ctx* ctx, int nfields, const igg_field* fields,
                     const int* dims_order, int ndims_order, void* stream, int flags);
+
+/* Prepared calls: validate the arguments, resolve the pointers and build the exchange plan ONCE, then repeat the same
+ * update_halo! with one cheap call per time step.  The reference has no such object; what it corresponds to is the
+ * steady state of `update_halo!` after its first call has allocated the buffers (ref: src/update_halo.jl:103-107,
+ * 126-148 allocate_bufs; src/CUDAExt/update_halo.jl:60-76), minus the per-call check_fields (:418-480), which a
+ * prepared call skips.  The fields (addresses, sizes, halowidths) must stay as they were when igg_prepare was called.
+ * igg_update_halo_prepared has the semantics of igg_update_halo (collective, `flags`, stream order) and may be
+ * captured into a CUDA graph with IGG_ASYNC.  Handles are released with igg_release_prepared (or simply dropped at
+ * igg_destroy: using a handle after its context is gone returns IGG_ERR_STATE). */
+typedef struct igg_prepared igg_prepared;
+int igg_prepare(igg_ctx* ctx, int nfields, const igg_field* fields, const int* dims_order, int ndims_order,
+                igg_prepared** out);
+int igg_update_halo_prepared(igg_prepared* call, void* stream, int flags);
+int igg_release_prepared(igg_prepared* call);
 
 /* igg_update_halo_noalloc -- no counterpart in the reference.
  * The same halo update for callers that are not allowed to allocate device memory (a host application whose own pool
@@ -205,9 +222,10 @@ typedef struct igg_plan_op {
 int igg_plan_describe(const igg_grid_desc* desc, int nfields, const igg_field* fields,
                       const int* dims_order, int ndims_order,
                       igg_plan_op* ops_out, int ops_cap, int* nops_out, int64_t* staging_bytes_out);
-/* The tile table the exchange kernel of `mode` (IGG_MODE_IPC_1PHASE or IGG_MODE_IPC_LL128) would walk for this call
+/* The tile table the exchange kernel would walk in `mode` (IGG_MODE_IPC_1PHASE or IGG_MODE_IPC_LL128) for this call
  * on this rank: `*ntiles_out` records of 80 bytes each (layout: struct TileRec in csrc/igg_internal.h; PUSH tiles
- * first, then LOCAL, then UNPACK).  `regions_out` (may be NULL) receives 4 x 27 numbers, indexed by neighbour offset
+ * first, then the x self-wraps (WRAPX) and the other LOCAL tiles, then UNPACK).  `mode` may also be
+ * IGG_MODE_IPC_AUTO.  `regions_out` (may be NULL) receives 4 x 27 numbers, indexed by neighbour offset
  * (ox+1) + 3(oy+1) + 9(oz+1): where that offset's staging slots start in the table's packed layout, how many bytes
  * of a staging half the offset needs, and the same two for its arrival flags.  (At run time every offset owns a
  * region whose position does not depend on the call; the launch shifts each offset's base accordingly.)
@@ -235,6 +253,14 @@ int igg_ctrl_selftest_run(void* handle, int me, int nprocs, const char* names, i
 int igg_debug_state(igg_ctx* ctx, uint64_t out[32]);
 int igg_trace_enable(igg_ctx* ctx, int on);
 int igg_trace_read(igg_ctx* ctx, uint64_t* out, int cap_blocks, int* nblocks_out);
+/* Host cost of issuing `n` stream-ordered prepared calls back to back from C: nanoseconds per call (for profiles). */
+int igg_debug_issue_loop(igg_prepared* call, void* stream, int n, double* ns_per_call_out);
+/* The timed loop of bench.py, issued from C as a compiled-language host (Julia `ccall` loop) would issue it: `steps`
+ * prepared calls, call i = calls[i % ncalls].  flags = IGG_ASYNC: one pair of CUDA events on `stream` around every
+ * call, us_out[i] = event time of call i in microseconds, *loop_us_out = (first event to last event) / steps.
+ * flags = IGG_SYNC: host clock around every host-synchronous call. */
+int igg_debug_timed_calls(igg_prepared** calls, int ncalls, void* stream, int steps, int flags, float* us_out,
+                          double* loop_us_out);
 /* Number of kernels this context has launched so far (the bench's `gpu_launches`). */
 int64_t igg_launch_count(const igg_ctx* ctx);
 /* Name of the kernel symbol the update path launches (for profiles). */

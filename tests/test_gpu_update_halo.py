@@ -417,3 +417,77 @@ def test_launch_counter_and_kernel_name():
     for _ in range(4):
         igg.update_halo(t)
     assert L.load().igg_launch_count(C.c_void_p(ctx)) == n0 + 4
+
+
+def test_prepared_calls_through_the_c_abi():
+    """igg_prepare / igg_update_halo_prepared: same bits as igg_update_halo, repeatedly, blocking and stream-ordered,
+    with `dims=` subsets, and a clean error once the context is gone."""
+    import ctypes as C
+    from igg_b200 import _lib as L
+    lib = L.load()
+    kw = dict(periodx=1, periody=1, periodz=1, overlaps=(4, 2, 2), halowidths=(2, 1, 1))
+    igg.init_global_grid(33, 17, 20, quiet=True, **kw)
+    (g,) = O.make_grids(1, 33, 17, 20, **kw)
+    gg = igg.global_grid()
+    shapes = [(33, 17, 20), (34, 17, 20)]
+    base = [O.random_bits_field(s, 8, 40 + i) for i, s in enumerate(shapes)]
+    s = torch.cuda.Stream()
+    sp = C.c_void_p(s.cuda_stream)
+    handles = []
+    for dims in [(3, 1, 2), (1,), (2, 3)]:
+        want = [a.copy(order="F") for a in base]
+        O.update_halo([g], [want], dims=dims)
+        ts = [igg.from_numpy(a) for a in base]
+        arr = (L.Field * 2)(*[L.make_field(t.data_ptr(), tuple(t.shape), gg.halowidths, 8) for t in ts])
+        d = (C.c_int * len(dims))(*dims)
+        h = C.c_void_p()
+        L.check(lib.igg_prepare(gg.ctx, 2, arr, d, len(dims), C.byref(h)))
+        handles.append(h)
+        for rep in range(4):
+            for t, a in zip(ts, base):
+                t.copy_(igg.from_numpy(a))
+            torch.cuda.synchronize()
+            L.check(lib.igg_update_halo_prepared(h, sp, L.IGG_SYNC if rep % 2 == 0 else L.IGG_ASYNC))
+            if rep % 2 == 0:          # host-synchronous: the halos are there on return, without any further wait
+                got = [t.clone() for t in ts]
+            else:
+                s.synchronize()
+                got = ts
+            for t, w in zip(got, want):
+                assert bits_equal(t, w), (dims, rep)
+    bad = (L.Field * 2)(L.make_field(ts[0].data_ptr(), shapes[0], gg.halowidths, 8), L.make_field(ts[0].data_ptr(), shapes[0], gg.halowidths, 8))
+    h2 = C.c_void_p()
+    assert lib.igg_prepare(gg.ctx, 2, bad, None, 0, C.byref(h2)) == L.IGG_ERR_FIELDS      # duplicates are still refused
+    L.check(lib.igg_release_prepared(handles.pop()))
+    igg.finalize_global_grid()
+    assert lib.igg_update_halo_prepared(handles[0], sp, L.IGG_SYNC) == L.IGG_ERR_STATE
+    for h in handles:
+        L.check(lib.igg_release_prepared(h))
+
+
+@pytest.mark.parametrize("blocking_env", ["spin", "sync"])
+def test_blocking_call_completion_paths(blocking_env, monkeypatch):
+    """The host-synchronous call waits either on a host-mapped word the kernel's last block writes (default) or with
+    cudaStreamSynchronize (IGG_BLOCKING=sync): on return the halos must be in memory either way, also for plans
+    with many more tiles than blocks and right after stream-ordered calls."""
+    monkeypatch.setenv("IGG_BLOCKING", blocking_env)
+    n = (96, 80, 72)
+    igg.init_global_grid(*n, periodx=1, periody=1, periodz=1, quiet=True)
+    (g,) = O.make_grids(1, *n, periodx=1, periody=1, periodz=1)
+    base = [O.random_bits_field(n, 8, 60 + i) for i in range(6)]
+    want = [a.copy(order="F") for a in base]
+    O.update_halo([g], [want])
+    ts = [igg.from_numpy(a) for a in base]
+    side = torch.cuda.Stream()
+    for rep in range(3):
+        for t, a in zip(ts, base):
+            t.copy_(igg.from_numpy(a))
+        torch.cuda.synchronize()
+        igg.update_halo(*ts[:3], blocking=False)
+        igg.update_halo(*ts)                      # blocking; returns when its launch is done
+        with torch.cuda.stream(side):             # a stream that is NOT ordered behind the call's stream
+            got = [t.clone() for t in ts]
+        side.synchronize()
+        for t, w in zip(got, want):
+            assert bits_equal(t, w), rep
+    igg.finalize_global_grid()

@@ -200,13 +200,23 @@ def test_error_paths():
     bad.neighbors[0][1] = L.IGG_PROC_NULL          # left = me, right = PROC_NULL
     with pytest.raises(L.IGGError, match="Incoherent neighbors in dimension 1"):
         L.plan_describe(bad, [fa])
-    # several ranks: an array made of halo cells only in an exchanged dimension is refused (interior ranks would
-    # have nothing to copy, and every rank must take part in a call or none)
-    two = L.make_desc((4, 8, 8), (2, 1, 1), (0, 0, 0), ((-1, -1, -1), (1, -1, -1)), (0, 0, 0), (4, 2, 2), (2, 1, 1), 0, 2, 0)
-    thin = L.make_field(0x1000, (4, 8, 8), (2, 1, 1), 8)
-    with pytest.raises(L.IGGError, match="has no interior cells in dimension 1"):
-        L.plan_describe(two, [thin])
-    L.plan_describe(two, [L.make_field(0x1000, (5, 8, 8), (2, 1, 1), 8)])      # one interior plane: fine
+
+
+THIN = [((4, 8, 8), (4, 2, 2), (2, 1, 1), [(4, 8, 8)]), ((4, 4, 8), (4, 4, 2), (2, 2, 1), [(4, 4, 8), (4, 5, 8)])]
+
+
+@pytest.mark.parametrize("topo", [(2, 1, 1), (3, 1, 1), (3, 2, 1), (2, 2, 2), (3, 3, 1)], ids=lambda t: "x".join(map(str, t)))
+@pytest.mark.parametrize("periods", [(0, 0, 0), (0, 0, 1)], ids=lambda p: "p" + "".join(map(str, p)))   # thin dims cannot be periodic
+@pytest.mark.parametrize("thin", THIN, ids=["x", "xy"])
+def test_arrays_without_interior_cells(topo, periods, thin):
+    """Arrays made of halo cells only in an exchanged dimension (size == 2 * halowidth): the reference accepts them
+    (has-halo predicate only, ref: src/update_halo.jl:239, src/shared.jl:220) and so does the single-phase plan -- a
+    rank in the middle of such a dimension has empty face boxes in the other dimensions, its neighbours' data all
+    arrives through the faces / edges of that dimension."""
+    gsz, ol, hw, shapes = thin
+    grids = O.make_grids(topo[0] * topo[1] * topo[2], *gsz, dimx=topo[0], dimy=topo[1], dimz=topo[2], periodx=periods[0],
+                         periody=periods[1], periodz=periods[2], overlaps=ol, halowidths=hw)
+    compare(grids, shapes, [hw] * len(shapes), 8)
 
 
 def test_c_ranges_match_reference_known_answers():

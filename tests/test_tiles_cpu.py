@@ -13,7 +13,7 @@ from igg_b200 import _lib as L
 from oracle import igg_oracle as O
 from test_plan_vs_oracle import desc_of, flat_bytes, rand_field
 
-PUSH, LOCAL, UNPACK, PUSH_LL, UNPACK_LL = 0, 1, 2, 6, 7
+PUSH, LOCAL, UNPACK, PUSH_LL, UNPACK_LL, WRAPX = 0, 1, 2, 6, 7, 8
 LINE, PAYLOAD = 128, 120
 OFFSETS = [(ox, oy, oz) for oz in (-1, 0, 1) for oy in (-1, 0, 1) for ox in (-1, 0, 1)]   # index = (ox+1)+3(oy+1)+9(oz+1)
 
@@ -41,6 +41,22 @@ def copy_rows(t, src, dst):
         dst[d:d + nb] = src[s:s + nb]
 
 
+def wrap_x(t, mem):
+    """wrapx_tile of the kernel: per (row, word) the low send word goes to the high halo and the high send word to the
+    low halo; high send = high halo - delta, low halo = low send - delta (delta in dst_sy)."""
+    W, delta = 1 << t.vec_log2, t.dst_sy
+    for r in range(t.nrows):
+        row = t.row0 + r
+        y, z = row % t.ny, row // t.ny
+        for c in range(t.ncols):
+            off = y * t.src_sy + z * t.src_sz + c * W
+            lo_send, hi_halo = t.src_off + off, t.dst_off + off
+            a = mem[lo_send:lo_send + W].copy()
+            b = mem[hi_halo - delta:hi_halo - delta + W].copy()
+            mem[hi_halo:hi_halo + W] = a
+            mem[lo_send - delta:lo_send - delta + W] = b
+
+
 def box_offset(t, pb):
     """box_seek of the kernel: payload byte pb -> byte offset in the field."""
     r, c = divmod(pb, t.ncols)
@@ -58,16 +74,18 @@ def run_tables(grids, fields_per_rank, hws, dims, mode, epoch=7):
         tables.append(tiles)
         stagings.append(np.full(max(stg, 1), 0xEE, dtype=np.uint8))
     kinds = {t.kind for tb in tables for t in tb}
-    assert kinds <= ({PUSH_LL, LOCAL, UNPACK_LL} if mode == L.IGG_MODE_IPC_LL128 else {PUSH, LOCAL, UNPACK})
+    assert kinds <= ({PUSH_LL, LOCAL, WRAPX, UNPACK_LL} if mode == L.IGG_MODE_IPC_LL128 else {PUSH, LOCAL, WRAPX, UNPACK})
     ep = np.frombuffer(np.uint64(epoch).tobytes(), dtype=np.uint8)
     for r, g in enumerate(grids):                       # everything that does not wait
         order = [t.kind for t in tables[r]]
-        assert order == sorted(order, key=lambda k: {PUSH: 0, PUSH_LL: 0, LOCAL: 1, UNPACK: 2, UNPACK_LL: 2}[k])
+        assert order == sorted(order, key=lambda k: {PUSH: 0, PUSH_LL: 0, WRAPX: 1, LOCAL: 1, UNPACK: 2, UNPACK_LL: 2}[k])
         for t in tables[r]:
             if t.kind == PUSH:
                 copy_rows(t, mem[r][t.field], stagings[peer_of(g, t.nbr)])
             elif t.kind == LOCAL:
                 copy_rows(t, mem[r][t.field], mem[r][t.field])
+            elif t.kind == WRAPX:
+                wrap_x(t, mem[r][t.field])
             elif t.kind == PUSH_LL:
                 W, nbytes, stg = 1 << t.vec_log2, t.dst_sy, stagings[peer_of(g, t.nbr)]
                 assert t.ncols % W == 0 and nbytes % W == 0 and t.dst_off % LINE == 0
@@ -111,7 +129,40 @@ CASES = [
     (8, (13, 9, 10), dict(periodx=1, periody=1, periodz=1), [(13, 9, 10)], None, 1, (2, 1)),
     (8, (13, 9, 10), dict(periodx=1, periody=1, periodz=1), [(13, 9, 10), (14, 9, 10)], None, 16, (3, 1, 2)),
     (4, (13, 9, 10), dict(periodx=1, periody=1, periodz=1), [(13, 9, 10)], None, 12, (3, 1, 2)),       # W = 4 < element
+    # the rank is its own x neighbour: the two x-faces of a field wrap together (WRAPX tiles)
+    (1, (13, 9, 10), dict(periodx=1, periody=1, periodz=1), [(13, 9, 10), (14, 9, 10)], None, 8, (3, 1, 2)),
+    (1, (16, 9, 10), dict(periodx=1, periodz=1, overlaps=(4, 2, 2), halowidths=(2, 1, 1)), [(16, 9, 10), (17, 10, 10)], None, 8, (3, 1, 2)),
+    (1, (40, 24, 20), dict(periodx=1, periody=1, periodz=1), [(40, 24, 20)], None, 4, (3, 1, 2)),      # several WRAPX tiles
+    (1, (13, 9, 10), dict(periodx=1, overlaps=(6, 2, 2), halowidths=(3, 1, 1)), [(13, 9, 10)], None, 2, (1,)),
+    (1, (13, 9, 10), dict(periodx=1, periody=1), [(13, 9, 10)], None, 1, (1, 2)),
+    (1, (13, 9, 10), dict(periodx=1, periody=1, periodz=1), [(13, 9, 10)], None, 12, (3, 1, 2)),
+    (1, (13, 9, 10), dict(periodx=1, periody=1, periodz=1, overlaps=(4, 2, 2), halowidths=(2, 1, 1)), [(13, 9, 10)], None, 16, (3, 1, 2)),
+    (1, (40, 30, 1), dict(periodx=1, periody=1), [(40, 30), (41, 30)], None, 8, (3, 1, 2)),
+    (1, (64, 1, 1), dict(periodx=1), [(64,), (65,)], None, 4, (3, 1, 2)),
+    (2, (13, 9, 10), dict(dimx=1, dimy=2, periodx=1, periody=1, periodz=1), [(13, 9, 10), (14, 9, 10)], None, 8, (3, 1, 2)),
+    (4, (13, 9, 10), dict(dimx=1, dimy=2, dimz=2, periodx=1, overlaps=(4, 2, 2), halowidths=(2, 1, 1)), [(13, 9, 10)], None, 4, (3, 1, 2)),
+    # more than 2 MiB staged per call: the fence protocol's tiles grow beyond 8 KiB
+    (2, (256, 256, 6), dict(dimx=1, dimy=1, dimz=2, periodx=1, periody=1, periodz=1), [(256, 256, 6)] * 3, None, 8, (3, 1, 2)),
 ]
+
+
+def test_fence_tiles_grow_with_the_call():
+    grids = O.make_grids(2, 256, 256, 6, dimx=1, dimy=1, dimz=2, periodx=1, periody=1, periodz=1)
+    cf = [L.make_field(0x10000 * (i + 1), (256, 256, 6), grids[0].halowidths, 8) for i in range(3)]
+    tiles, _ = L.plan_tiles(desc_of(grids[0]), cf, (3, 1, 2), L.IGG_MODE_IPC_1PHASE)
+    assert 8192 < max((t.nrows * t.ncols) << t.vec_log2 for t in tiles if t.kind == PUSH) <= 16384
+    few, _ = L.plan_tiles(desc_of(grids[0]), cf[:1], (3, 1, 2), L.IGG_MODE_IPC_1PHASE)
+    assert max((t.nrows * t.ncols) << t.vec_log2 for t in few if t.kind == PUSH) <= 8192
+    # the default mode picks LL128 for this call (3 MiB staged, below the 8 MiB threshold)
+    auto, _ = L.plan_tiles(desc_of(grids[0]), cf, (3, 1, 2), L.IGG_MODE_IPC_AUTO)
+    assert any(t.kind == PUSH_LL for t in auto) and not any(t.kind == PUSH for t in auto)
+
+
+def test_wrapx_tiles_are_emitted():
+    """The single-rank periodic cases above must actually go through WRAPX tiles (not plain LOCAL copies)."""
+    (g,) = O.make_grids(1, 13, 9, 10, periodx=1, periody=1, periodz=1)
+    tiles, _ = L.plan_tiles(desc_of(g), [L.make_field(0x10000, (13, 9, 10), g.halowidths, 8)], (3, 1, 2), L.IGG_MODE_IPC_AUTO)
+    assert sum(t.kind == WRAPX for t in tiles) >= 1 and all(t.kind in (WRAPX, LOCAL) for t in tiles)
 
 
 def struct_field(shape, elsize, seed):
@@ -167,7 +218,7 @@ def test_every_tile_stays_inside_its_offsets_region(case, mode):
         for o in range(27):
             assert reg["byte_pack"][o] == sum(reg["byte_need"][:o]) and reg["flag_pack"][o] == sum(reg["flag_need"][:o])
         for t in tiles:
-            if t.kind == LOCAL:
+            if t.kind in (LOCAL, WRAPX):
                 continue
             o = 26 - t.nbr if t.kind in (PUSH, PUSH_LL) else t.nbr
             lo, hi = staged_range(t)
@@ -179,7 +230,7 @@ def test_every_tile_stays_inside_its_offsets_region(case, mode):
 
 
 @pytest.mark.parametrize("mode", [L.IGG_MODE_IPC_1PHASE, L.IGG_MODE_IPC_LL128], ids=["fence", "ll128"])
-@pytest.mark.parametrize("ci,case", [(i, c) for i, c in G.cases() if c["nprocs"] > 1], ids=[c["name"] for _, c in G.cases() if c["nprocs"] > 1])
+@pytest.mark.parametrize("ci,case", list(G.cases()), ids=[c["name"] for _, c in G.cases()])
 def test_tile_tables_match_golden(ci, case, mode):
     grids = O.make_grids(case["nprocs"], *case["grid"], **G.kwargs(case))      # grid descriptions only
     hws = G.halowidths(case, grids[0].halowidths)
