@@ -12,7 +12,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(HERE)
 CSRC = os.path.join(HERE, "csrc")
 OUT = os.path.join(HERE, "libigg_b200.so")
-SOURCES = ["plan.cpp", "ctrl_shm.cpp", "halo_kernel.cu", "ctx.cu", "nccl_path.cu", "noalloc.cu", "diffusion3d.cu"]
+SOURCES = ["plan.cpp", "ctrl_shm.cpp", "halo_kernel.cu", "ctx.cu", "ll128_check.cu", "nccl_path.cu", "noalloc.cu", "diffusion3d.cu"]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "-Xcompiler", "-fPIC,-Wall,-Wno-unused-function",
          "-I", os.path.join(ROOT, "include"), "-I", CSRC]

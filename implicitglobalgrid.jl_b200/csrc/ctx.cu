@@ -90,6 +90,8 @@ struct igg_ctx {
     unsigned long long* d_done = nullptr;
     unsigned long long ticket = 0;              // value the next host-synchronous launch stores into *h_done
     bool spin_wait = true;                      // IGG_BLOCKING=sync: wait with cudaStreamSynchronize instead
+    bool ll128_ok = true;                       // false: link check or self-test said LL128 lines may tear -> fence protocol only
+    unsigned long long ll128_test[3] = {0, 0, 0};   // self-test: torn line images, time-outs, line images checked
     ControlPlane cp;
     std::string shm_name;
     std::vector<Peer> peers;
@@ -391,6 +393,9 @@ static Plan* find_or_build_plan(igg_ctx* ctx, int nfields, const igg_field* fiel
             break;
         }
     }
+    // Launch constants for the layout as it is now (ensure_layout uploads them again whenever the layout moves).
+    rc = upload_plan_dev(ctx, *plan);
+    if (rc) { cudaFree(plan->d_plan); cudaFree(plan->d_wrap_tiles); *rc_out = rc; return nullptr; }
     ctx->plans.push_back(std::move(plan));
     *rc_out = IGG_OK;
     return ctx->plans.back().get();
@@ -446,6 +451,68 @@ static int wait_done(igg_ctx* ctx, cudaStream_t stream, unsigned long long ticke
     }
     CU(cudaStreamSynchronize(stream));
     return check_status(ctx);
+}
+
+// Is LL128 safe between these ranks?  (1) Every peer must sit behind NVLink: a PCIe peer path may split a 128-byte
+// warp store (native peer atomics are the attribute that tells the two apart).  (2) The assumption itself is put to
+// the test between ring neighbours (ll128_check.cu).  The verdicts are combined over all ranks, so that every rank
+// ends up with the same protocol; a failure downgrades the context to the fence protocol and says so once.
+// IGG_LL128_SELFTEST=0 skips the test, IGG_LL128_SELFTEST_FAIL=1 makes it fail on purpose (to exercise the fallback).
+static int check_ll128(igg_ctx* ctx) {
+    const int n = ctx->g.nprocs, me = ctx->g.me;
+    bool ok = true, same_gpu = false;
+    char why[160] = "";
+    for (int r = 0; r < n; ++r) {
+        if (r == me) continue;
+        const Peer& p = ctx->peers[r];
+        if (p.device == ctx->device && p.proc_nonce == process_nonce()) { same_gpu = true; continue; }
+        int native = 0;
+        if (p.device != ctx->device &&
+            cudaDeviceGetP2PAttribute(&native, cudaDevP2PAttrNativeAtomicSupported, ctx->device, p.device) == cudaSuccess) {
+            if (!native) { ok = false; snprintf(why, sizeof(why), "the peer path to rank %d (device %d) is not NVLink", r, p.device); }
+        } else {
+            cudaGetLastError();
+        }
+    }
+    const char* st = getenv("IGG_LL128_SELFTEST");
+    const bool run_test = ok && n > 1 && !same_gpu && !(st && st[0] == '0');
+    const bool corrupt = getenv("IGG_LL128_SELFTEST_FAIL") && getenv("IGG_LL128_SELFTEST_FAIL")[0] == '1';
+    int rc = ctx->cp.barrier();                 // every rank has mapped every control segment
+    if (rc) return rc;
+    if (run_test) {
+        const int lines = 4096, rounds = 32;    // 512 KiB of the (still unused) arrival-flag area as scratch
+        const int right = (me + 1) % n;
+        rc = ll128_selftest(ctx->peers[right].ctrl.ptr + kFlagsOff, ctx->ctrl + kFlagsOff, lines, rounds, corrupt,
+                            5ull * 1000000000ull, ctx->ll128_test);
+        if (rc) return rc;
+        if (ctx->ll128_test[0] || ctx->ll128_test[1]) {
+            ok = false;
+            snprintf(why, sizeof(why), "self-test: %llu torn line images, %llu time-outs in %llu line images",
+                     ctx->ll128_test[0], ctx->ll128_test[1], ctx->ll128_test[2]);
+        }
+        rc = ctx->cp.barrier();                 // nobody writes into my scratch any more
+        if (rc) return rc;
+        CU(cudaMemset(ctx->ctrl + kFlagsOff, 0, (size_t)lines * 128));
+        CU(cudaDeviceSynchronize());
+    }
+    SegPayload mine;
+    std::memset(&mine, 0, sizeof(mine));
+    mine.status = ok ? 1 : 0;
+    snprintf(mine.msg, sizeof(mine.msg), "%s", why);
+    std::vector<char> all;
+    rc = ctx->cp.allgather(&mine, all);
+    if (rc) return rc;
+    for (int r = 0; r < n; ++r) {
+        SegPayload q;
+        std::memcpy(&q, all.data() + (size_t)r * sizeof(SegPayload), sizeof(q));
+        if (!q.status) {
+            if (ctx->ll128_ok && me == 0)
+                fprintf(stderr, "libigg_b200: LL128 is not safe on this system (rank %d: %s); using the fence protocol.\n", r, q.msg);
+            ctx->ll128_ok = false;
+        }
+    }
+    if (!ctx->ll128_ok && (ctx->mode == IGG_MODE_IPC_AUTO || ctx->mode == IGG_MODE_IPC_LL128)) ctx->mode = IGG_MODE_IPC_1PHASE;
+    return IGG_OK;
 }
 
 // ---- C ABI -------------------------------------------------------------------------------------------------------
@@ -566,6 +633,8 @@ int igg_bootstrap_import(igg_ctx* ctx, const void* all_blobs, int nprocs) {
     }
     int rc = ctx->cp.attach(names);
     if (rc) return rc;
+    rc = check_ll128(ctx);
+    if (rc) return rc;
     ctx->bootstrapped = true;
     return IGG_OK;
 }
@@ -576,6 +645,9 @@ int igg_set_mode(igg_ctx* ctx, int mode) {
         return fail(IGG_ERR_ARG, "igg_set_mode: unknown mode %d.", mode);
     if (mode == IGG_MODE_NCCL_3PHASE && ctx->g.nprocs > 1 && !ctx->nccl)
         return fail(IGG_ERR_STATE, "igg_set_mode: call igg_nccl_init before selecting IGG_MODE_NCCL_3PHASE.");
+    if (!ctx->ll128_ok && mode == IGG_MODE_IPC_LL128)
+        return fail(IGG_ERR_UNSUPPORTED, "igg_set_mode: LL128 was found unsafe on this system at bootstrap (link check / self-test).");
+    if (!ctx->ll128_ok && mode == IGG_MODE_IPC_AUTO) mode = IGG_MODE_IPC_1PHASE;
     // The two IPC protocols stage in regions of their own (ensure_layout), so switching needs no clean-up.
     ctx->mode = mode;
     return IGG_OK;
@@ -860,14 +932,15 @@ int igg_debug_timed_calls(igg_prepared** calls, int ncalls, void* stream_v, int 
     int rc = IGG_OK;
     for (auto& e : ev)
         if (cudaEventCreate(&e) != cudaSuccess) rc = fail(IGG_ERR_CUDA, "igg_debug_timed_calls: cudaEventCreate failed.");
+    const bool per_call = !(flags & 2);        // flags | 2: only the first and the last event are recorded
     for (int i = 0; i < steps && !rc; ++i) {
-        cudaEventRecord(ev[2 * i], stream);
+        if (per_call || i == 0) cudaEventRecord(ev[2 * i], stream);
         rc = igg_update_halo_prepared(calls[i % ncalls], stream_v, IGG_ASYNC);
-        cudaEventRecord(ev[2 * i + 1], stream);
+        if (per_call || i == steps - 1) cudaEventRecord(ev[2 * i + 1], stream);
     }
     if (!rc && cudaStreamSynchronize(stream) != cudaSuccess) rc = fail(IGG_ERR_CUDA, "igg_debug_timed_calls: %s", cudaGetErrorString(cudaGetLastError()));
     if (!rc) {
-        for (int i = 0; i < steps; ++i) {
+        for (int i = 0; i < steps && per_call; ++i) {
             float ms = 0;
             cudaEventElapsedTime(&ms, ev[2 * i], ev[2 * i + 1]);
             us_out[i] = ms * 1e3f;
@@ -1046,7 +1119,7 @@ int igg_debug_state(igg_ctx* ctx, uint64_t out[32]) {
     out[28] = st.blocks_done;
     out[29] = (uint64_t)ctx->staging_half;
     out[30] = (uint64_t)ctx->launches;
-    out[31] = 0;
+    out[31] = (uint64_t)ctx->mode | ((uint64_t)(ctx->ll128_ok ? 1 : 0) << 8) | (ctx->ll128_test[2] << 16);
     return IGG_OK;
 }
 

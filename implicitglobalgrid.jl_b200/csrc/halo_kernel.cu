@@ -547,10 +547,13 @@ int halo_kernel_max_coresident_blocks(int device) {
 }
 
 int launch_halo_kernel(const KParams& p, int grid, void* stream, bool ll128) {
-    // IGG_PDL=1 switches programmatic dependent launch on.  Measured (graph replay, cfg2): it hides launch latency for
-    // tiny updates (y-faces only: 3.44 -> 2.77 us) but the early-scheduled next grid slows a full update down
-    // (1 GPU 9.7 -> 12.3 us, 2 GPUs 15.6 -> 18.2 us), so plain stream order is the default.
-    static const bool pdl = [] { const char* e = getenv("IGG_PDL"); return e && e[0] == '1'; }();
+    // Programmatic dependent launch: the next grid is scheduled while this one still runs and waits at
+    // griddepcontrol.wait, which hides its launch latency.  Default: on for launches that exchange with no other rank
+    // (no exchange state to read, nothing to spin on: cfg2 on one GPU 10.3 -> 8.1 us per stream-ordered call, 8.8 ->
+    // 7.9 us replayed from a graph), off for launches whose blocks wait for a neighbour (an early-scheduled grid takes
+    // SM slots from a grid that is still pushing: measured slower in round 1).  IGG_PDL=1 / 0 forces it on / off.
+    static const int pdl_env = [] { const char* e = getenv("IGG_PDL"); return !e ? -1 : (e[0] == '1' ? 1 : 0); }();
+    const bool pdl = pdl_env >= 0 ? pdl_env == 1 : p.state == nullptr;
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)grid);
     cfg.blockDim = dim3(kThreads);

@@ -227,6 +227,10 @@ void nccl_free(NcclPath* np);
 int  nccl_phase(NcclPath* np, const igg_grid_desc& g, int nfields, const igg_field* fields, int d, int max_blocks,
                 const KParams& proto, void* stream, int64_t* launches);
 
+// ---- LL128 self-test (ll128_check.cu) ----------------------------------------------------------------------
+int  ll128_selftest(char* to_peer, const char* mine, int lines, int rounds, bool corrupt, unsigned long long timeout_ns,
+                    unsigned long long out[3]);
+
 // ---- kernel launcher (halo_kernel.cu) ----------------------------------------------------------------------
 int  halo_kernel_max_coresident_blocks(int device);     // occupancy * SM count
 int  launch_halo_kernel(const KParams& p, int grid, void* stream, bool ll128 = false);

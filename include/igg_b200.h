@@ -249,7 +249,8 @@ int igg_ctrl_selftest_run(void* handle, int me, int nprocs, const char* names, i
  * records (8 words per block, `*nblocks_out` blocks). */
 /* Debug: the device-resident exchange state after synchronising the device: out[0] = exchange launches completed,
  * out[1..27] = exchanges completed per neighbour offset, out[28] = blocks-done counter (0 between launches),
- * out[29] = bytes of one staging half, out[30] = launches issued by the host. */
+ * out[29] = bytes of one staging half, out[30] = launches issued by the host, out[31] = current igg_mode (bits 0-7),
+ * "LL128 passed the bootstrap link check and self-test" (bit 8), line images the self-test checked (bits 16..). */
 int igg_debug_state(igg_ctx* ctx, uint64_t out[32]);
 int igg_trace_enable(igg_ctx* ctx, int on);
 int igg_trace_read(igg_ctx* ctx, uint64_t* out, int cap_blocks, int* nblocks_out);
@@ -258,6 +259,7 @@ int igg_debug_issue_loop(igg_prepared* call, void* stream, int n, double* ns_per
 /* The timed loop of bench.py, issued from C as a compiled-language host (Julia `ccall` loop) would issue it: `steps`
  * prepared calls, call i = calls[i % ncalls].  flags = IGG_ASYNC: one pair of CUDA events on `stream` around every
  * call, us_out[i] = event time of call i in microseconds, *loop_us_out = (first event to last event) / steps.
+ * flags = IGG_ASYNC | 2: the same loop with only the first and the last event (us_out is left alone).
  * flags = IGG_SYNC: host clock around every host-synchronous call. */
 int igg_debug_timed_calls(igg_prepared** calls, int ncalls, void* stream, int steps, int flags, float* us_out,
                           double* loop_us_out);

@@ -28,7 +28,12 @@ ap = argparse.ArgumentParser()
 ap.add_argument("--out", default=None)
 ap.add_argument("--steps", type=int, default=400)
 ap.add_argument("--only", default="")
+ap.add_argument("--modes", default="ipc,nccl", help="comma list of ipc (= the default, auto), auto, ll128, fence, nccl")
+ap.add_argument("--dims", default="", help="dimx,dimy,dimz to force a process grid (e.g. 1,1,2: the z-faces cross NVLink)")
+ap.add_argument("--nvl", type=float, default=770.0, help="NVLink GB/s per direction used for the roofline")
 args = ap.parse_args()
+MODES = tuple(m for m in args.modes.split(",") if m)
+FORCED = dict(zip(("dimx", "dimy", "dimz"), (int(x) for x in args.dims.split(",")))) if args.dims else {}
 
 world = int(os.environ.get("WORLD_SIZE", "1"))
 rank = int(os.environ.get("RANK", "0"))
@@ -36,7 +41,7 @@ torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", "0")))
 if world > 1:
     os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
     dist.init_process_group("cpu:gloo,cuda:nccl", device_id=torch.device("cuda", torch.cuda.current_device()))
-NVL, HBM = 770.0, 6555.5
+NVL, HBM = args.nvl, 6555.5
 results = []
 
 
@@ -78,9 +83,11 @@ def halo_bytes(g, shapes, hws, el):
     return tot, nvl
 
 
-def time_update(name, gsz, kw, shapes, dtype, hws=None, ring_bytes=3.3e9, modes=("ipc", "nccl")):
-    if args.only and args.only not in name:
+def time_update(name, gsz, kw, shapes, dtype, hws=None, ring_bytes=3.3e9, modes=None):
+    if args.only and not any(o in name for o in args.only.split(",")):
         return
+    modes = MODES if modes is None else tuple(m for m in MODES if m != "nccl")
+    kw = dict(kw, **{k: v for k, v in FORCED.items() if gsz[("dimx", "dimy", "dimz").index(k)] > 1})
     igg.init_global_grid(*gsz, quiet=True, **kw)
     g = igg.global_grid()
     el = torch.empty((), dtype=dtype).element_size()
@@ -112,7 +119,7 @@ def time_update(name, gsz, kw, shapes, dtype, hws=None, ring_bytes=3.3e9, modes=
         K = args.steps
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         graph = None
-        if mode == "ipc":
+        if mode != "nccl":
             graph = torch.cuda.CUDAGraph()
             with torch.cuda.graph(graph, stream=stream):
                 for i in range(K):
@@ -148,6 +155,8 @@ def time_update(name, gsz, kw, shapes, dtype, hws=None, ring_bytes=3.3e9, modes=
 
 def time_gather():
     if args.only and "cfg5a" not in args.only:
+        return
+    if FORCED:
         return
     n = 256
     igg.init_global_grid(n, n, n, quiet=True)

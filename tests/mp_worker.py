@@ -22,9 +22,10 @@ import igg_b200 as igg  # noqa: E402
 from oracle import igg_oracle as O  # noqa: E402
 
 TDT = {1: torch.uint8, 2: torch.int16, 4: torch.int32, 8: torch.int64}
-# The IPC protocol under test: contexts start in the one IGG_MODE names ("fence", else the default LL128); after a
+# The IPC mode under test: contexts start in the one IGG_MODE names ("fence", "ll128", else the default "auto", which
+# picks one of the two per call by size -- run it with a small IGG_BULK_THRESHOLD so that both get used); after a
 # detour through the NCCL comparison path the worker goes back to the same one.
-IPC_MODE = "fence" if os.environ.get("IGG_MODE") == "fence" else "ll128"
+IPC_MODE = os.environ.get("IGG_MODE") if os.environ.get("IGG_MODE") in ("fence", "ll128") else "auto"
 
 
 def case_list(n):
@@ -59,6 +60,20 @@ def main():
     import golden_cases as G
     for gi, case in G.cases(n):
         igg.init_global_grid(*case["grid"], quiet=True, **G.kwargs(case))
+        # The bootstrap's LL128 link check + self-test: passed (and really ran) unless the run forces it to fail
+        # (IGG_LL128_SELFTEST_FAIL=1), in which case the context must have fallen back to the fence protocol.
+        import ctypes as C
+        from igg_b200 import _lib as L
+        st = (C.c_uint64 * 32)()
+        L.check(L.load().igg_debug_state(igg.global_grid().ctx, st))
+        mode, ll_ok, checked = int(st[31]) & 0xff, (int(st[31]) >> 8) & 1, int(st[31]) >> 16
+        if os.environ.get("IGG_LL128_SELFTEST_FAIL") == "1":
+            if ll_ok or mode != L.IGG_MODE_IPC_1PHASE:
+                ok = False
+                print(f"FALLBACK NOT TAKEN rank {me}: mode {mode}, ll128_ok {ll_ok}", flush=True)
+        elif not ll_ok or checked < 4096 or mode != {"fence": 0, "ll128": 2, "auto": 3}[IPC_MODE]:
+            ok = False
+            print(f"LL128 SELF-TEST rank {me}: mode {mode}, ll128_ok {ll_ok}, {checked} line images checked", flush=True)
         hws = G.halowidths(case, igg.global_grid().halowidths)
         for rep in range(2):
             fields = [igg.from_numpy(a) for a in G.arrays(gi, me, "in")]
@@ -182,10 +197,13 @@ def main():
         gsz, kw = (13, 9, 10), dict(periodx=1, periody=1, periodz=1)
         grids = O.make_grids(n, *gsz, **kw)
         igg.init_global_grid(*gsz, quiet=True, **kw)
-        shp = {"A": (13, 9, 10), "B": (14, 9, 10), "C": (13, 9, 11)}
+        # D is big enough for the fence protocol when the worker runs in "auto" mode with IGG_BULK_THRESHOLD=16384: the
+        # two protocols then alternate on one context (each has staging regions of its own).
+        shp = {"A": (13, 9, 10), "B": (14, 9, 10), "C": (13, 9, 11), "D": (13, 64, 48)}
         dev = {k: igg.zeros(s, dtype=torch.int64) for k, s in shp.items()}
         seq = [("A", (1,)), ("AB", (3, 1, 2)), ("B", (2,)), ("A", (3, 1, 2)), ("ABC", (1, 3)), ("C", (3,)),
                ("BC", (2, 1)), ("A", (1,)), ("ABC", (3, 1, 2)), ("B", (3, 1, 2))] * 2
+        seq += [("D", (3, 1, 2)), ("A", (3, 1, 2)), ("D", (1,)), ("D", (3, 1, 2)), ("A", (1,)), ("D", (2, 3))]
         for k, (names, dims) in enumerate(seq):
             host = {nm: O.random_bits_field(shp[nm], 8, 5000 + 100 * k + 10 * me + i) for i, nm in enumerate(names)}
             torch.cuda.synchronize()
