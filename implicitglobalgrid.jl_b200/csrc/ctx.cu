@@ -714,6 +714,7 @@ static int launch_plan(igg_ctx* ctx, Plan* plan, int nfields, const igg_field* f
     p.notify = nullptr;
     p.notify_value = 0;
     p.fin_counter = &state->blocks_finished;
+    p.bulk = plan->has_bulk ? 1 : 0;
     static const bool wx_params = !(std::getenv("IGG_WX_PARAMS") && std::atoi(std::getenv("IGG_WX_PARAMS")) == 0);
     // (Measured and dropped: letting the WRAPX blocks sleep 400-1200 ns so that the contiguous tiles' loads get out
     // before the strided flood -- 8.62 / 8.76 / 9.01 us against 8.64 us per cfg2 update, cold L2.)

@@ -83,6 +83,7 @@ __device__ __forceinline__ TileRec load_tile(const TileRec* g) {
     t.vec_log2 = (uint8_t)((e.x >> 16) & 0xffu);
     t.kind = (uint8_t)(e.x >> 24);
     t.nbr = (uint8_t)(e.y & 0xffu);
+    t.bulk = (uint8_t)((e.y >> 8) & 0xffu);
     t.flag_idx = e.z;
     return t;
 }
@@ -99,7 +100,8 @@ __device__ __forceinline__ TileRec get_tile(const KParams& p, int ti) {
         t.src_off = w.src_off; t.dst_off = w.dst_off; t.src_sy = w.sy; t.src_sz = w.sz; t.dst_sy = w.delta; t.dst_sz = 0;
         t.row0 = ((uint32_t)j - w.tile0) * w.rows_per_tile;
         t.nrows = min(w.rows_per_tile, w.rows - t.row0);
-        t.ncols = w.ncols; t.ny = w.ny; t.field = w.field; t.vec_log2 = w.vec_log2; t.kind = (uint8_t)kOpWrapX; t.nbr = 0; t.flag_idx = 0;
+        t.ncols = w.ncols; t.ny = w.ny; t.field = w.field; t.vec_log2 = w.vec_log2; t.kind = (uint8_t)kOpWrapX; t.nbr = 0;
+        t.bulk = 0; t.flag_idx = 0;
         return t;
     }
     return load_tile(p.tiles + ti);
@@ -251,6 +253,90 @@ __global__ void __launch_bounds__(kThreads) igg_wrap_lines_kernel(const TileRec*
     }
 }
 
+// ---- bulk-copy pipeline (fence kernel): global -> shared -> global with cp.async.bulk (TMA unit) ------------------
+// For tiles of long contiguous rows (the y/z faces of the bandwidth regime: 2 KiB - 512 KiB runs) one thread of the
+// block moves the tile through a ring of shared-memory stages: bulk loads complete on an mbarrier per stage, bulk
+// stores are committed as groups.  No register traffic, 48 KiB in flight per block, and the other warps of the block
+// are free for the next tile.  Sources and destinations may be local memory or a peer GPU's (CUDA-IPC mapping).
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(unsigned long long* b) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(b)) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(unsigned long long* b, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(b)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long* b, uint32_t parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "WAIT_%=:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra DONE_%=;\n"
+        "bra WAIT_%=;\n"
+        "DONE_%=:\n"
+        "}" ::"r"(smem_u32(b)), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void* smem, const void* gmem, uint32_t bytes, unsigned long long* b) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(smem_u32(smem)), "l"(gmem), "r"(bytes), "r"(smem_u32(b)) : "memory");
+}
+__device__ __forceinline__ void bulk_s2g(void* gmem, const void* smem, uint32_t bytes) {
+    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gmem), "r"(smem_u32(smem)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_read0() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait0() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async;" ::: "memory"); }
+
+// The geometry of a tile, by value (a TileRec reference would force the caller's record into local memory).
+struct BulkTile { int64_t ssy, ssz, dsy, dsz; uint32_t row0, nrows, ncols, ny; };
+// Chunk c of a tile: `nr` rows starting at tile row r0, `bytes` bytes each, from byte `off` of the row.
+struct BulkChunk { uint32_t r0, nr, off, bytes; };
+__device__ __forceinline__ BulkChunk bulk_chunk(uint32_t nrows, uint32_t c, uint32_t rowb, uint32_t rows_per_chunk, uint32_t segs) {
+    BulkChunk k;
+    if (segs > 1) { k.r0 = c / segs; k.nr = 1; k.off = (c - k.r0 * segs) * kBulkStageBytes; k.bytes = min((uint32_t)kBulkStageBytes, rowb - k.off); }
+    else { k.r0 = c * rows_per_chunk; k.nr = min(rows_per_chunk, nrows - k.r0); k.off = 0; k.bytes = rowb; }
+    return k;
+}
+__device__ __forceinline__ int64_t bulk_row_off(uint32_t row, uint32_t ny, int64_t sy, int64_t sz) {
+    uint32_t z = 0, y = row;
+    if (row >= ny) { z = row / ny; y = row - z * ny; }
+    return (int64_t)y * sy + (int64_t)z * sz;
+}
+
+// Moves one tile; called by ONE thread.  `phase`: parity bit per stage, carried from tile to tile (returned).  On
+// return all stores of the tile are complete (their writes performed), so the caller may release the tile or let the
+// block end.
+__device__ __noinline__ uint32_t bulk_copy_tile(const BulkTile t, const char* __restrict__ src, char* __restrict__ dst,
+                                                unsigned char* stages, unsigned long long* mbar, uint32_t phase) {
+    const uint32_t rowb = t.ncols << 4;
+    uint32_t rows_per_chunk = 1, segs = 1;
+    if (rowb >= (uint32_t)kBulkStageBytes) segs = (rowb + kBulkStageBytes - 1) / kBulkStageBytes;
+    else rows_per_chunk = kBulkStageBytes / rowb;
+    const uint32_t nchunks = segs > 1 ? t.nrows * segs : (t.nrows + rows_per_chunk - 1) / rows_per_chunk;
+    for (uint32_t c = 0; c < nchunks + (kBulkStages - 1); ++c) {
+        if (c < nchunks) {
+            const uint32_t s = c % kBulkStages;
+            if (c >= (uint32_t)kBulkStages) bulk_wait_read0();      // the store that last used this stage has read it
+            const BulkChunk k = bulk_chunk(t.nrows, c, rowb, rows_per_chunk, segs);
+            mbar_expect_tx(mbar + s, k.nr * k.bytes);
+            for (uint32_t q = 0; q < k.nr; ++q)
+                bulk_g2s(stages + s * kBulkStageBytes + q * k.bytes, src + bulk_row_off(t.row0 + k.r0 + q, t.ny, t.ssy, t.ssz) + k.off, k.bytes, mbar + s);
+        }
+        if (c >= (uint32_t)(kBulkStages - 1)) {
+            const uint32_t d = c - (kBulkStages - 1), s = d % kBulkStages;
+            mbar_wait(mbar + s, (phase >> s) & 1u);
+            phase ^= 1u << s;
+            const BulkChunk k = bulk_chunk(t.nrows, d, rowb, rows_per_chunk, segs);
+            for (uint32_t q = 0; q < k.nr; ++q)
+                bulk_s2g(dst + bulk_row_off(t.row0 + k.r0 + q, t.ny, t.dsy, t.dsz) + k.off, stages + s * kBulkStageBytes + q * k.bytes, k.bytes);
+            bulk_commit();
+        }
+    }
+    bulk_wait0();
+    return phase;
+}
+
 // ---- IGG_MODE_IPC_LL128: line-formatted staging (see igg_internal.h) -------------------------------------------
 __device__ __forceinline__ void st_volatile_v2(char* p, unsigned long long lo, unsigned long long hi) {
     asm volatile("st.volatile.global.v2.u64 [%0], {%1, %2};" ::"l"(p), "l"(lo), "l"(hi) : "memory");
@@ -385,6 +471,13 @@ __device__ __forceinline__ void halo_exchange_body(const KParams& p) {
     __shared__ const char* s_unpack[IGG_NOFFSETS];    // staging half of mine the neighbour at offset o stores into
     __shared__ unsigned long long* s_rflags[IGG_NOFFSETS];
     __shared__ int s_lflag_delta[IGG_NOFFSETS];
+    __shared__ __align__(8) unsigned long long s_mbar[kBulkStages];
+    extern __shared__ __align__(128) unsigned char s_stages[];      // kBulkStages * kBulkStageBytes when p.bulk
+    uint32_t bulk_phase = 0;
+    if (p.bulk && threadIdx.x == 0) {                 // only thread 0 ever touches the barriers and the stages
+        for (int k = 0; k < kBulkStages; ++k) mbar_init(&s_mbar[k]);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
     // Optional per-block timeline (igg_trace_enable): [0] globaltimer at start, then SM clock at [1] start,
     // [2] first tile record loaded, [3] first copy issued, [4] first push flagged, [5] first flag seen, [6] end.
 #define IGG_TRACE(k) do { if (p.trace && threadIdx.x == 0) p.trace[(size_t)blockIdx.x * 8 + (k)] = (unsigned long long)clock64(); } while (0)
@@ -454,6 +547,38 @@ __device__ __forceinline__ void halo_exchange_body(const KParams& p) {
             }
             if (!ok && (threadIdx.x & 31u) == 0) *reinterpret_cast<volatile int*>(p.status) = IGG_ERR_TIMEOUT;
             if (first) IGG_TRACE(5);
+        } else if (t.bulk && p.bulk && (!LL || t.kind == IGG_OP_LOCAL)) {
+            // Long contiguous rows: thread 0 drives the bulk-copy pipeline, the other warps go on to the next tile.
+            if (threadIdx.x == 0) {
+                const BulkTile bt = {t.src_sy, t.src_sz, t.dst_sy, t.dst_sz, t.row0, t.nrows, t.ncols, t.ny};
+                if (!LL && t.kind == IGG_OP_UNPACK) {
+                    const unsigned long long* flag = p.local_flags + ((long long)t.flag_idx + s_lflag_delta[t.nbr]);
+                    unsigned long long t0 = 0;
+                    unsigned int spins = 0;
+                    while (ld_acquire_sys(flag) < s_epoch) {
+                        if ((++spins & 0x3ff) == 0) {
+                            const unsigned long long now = globaltimer_ns();
+                            if (t0 == 0) t0 = now;
+                            else if (now - t0 > p.timeout_ns) { *reinterpret_cast<volatile int*>(p.status) = IGG_ERR_TIMEOUT; break; }
+                        }
+                    }
+                    if (first) IGG_TRACE(5);
+                    fence_proxy_async();      // what the acquire made visible to this thread, the bulk loads must see too
+                    bulk_phase = bulk_copy_tile(bt, s_unpack[t.nbr] + t.src_off, static_cast<char*>(p.field[t.field]) + t.dst_off, s_stages, s_mbar, bulk_phase);
+                } else {
+                    const char* src = static_cast<const char*>(p.field[t.field]) + t.src_off;
+                    char* dst = (!LL && t.kind == IGG_OP_PUSH) ? s_push[t.nbr] + t.dst_off : static_cast<char*>(p.field[t.field]) + t.dst_off;
+                    bulk_phase = bulk_copy_tile(bt, src, dst, s_stages, s_mbar, bulk_phase);
+                    if (!LL && t.kind == IGG_OP_PUSH) {
+                        // the tile's bulk stores are complete: order them before the flag for the neighbour
+                        fence_proxy_async();
+                        fence_acq_rel_sys();
+                        st_relaxed_sys(s_rflags[t.nbr] + t.flag_idx, s_epoch);
+                        if (first) IGG_TRACE(4);
+                    }
+                }
+                if (first) IGG_TRACE(3);
+            }
         } else if (!LL && t.kind == IGG_OP_UNPACK) {
             // Wait until the neighbour has flagged this very tile (it flags each tile right after storing it).
             if (threadIdx.x == 0) {
@@ -540,8 +665,11 @@ __global__ void __launch_bounds__(kThreads, kBlocksPerSM) igg_halo_exchange_ll12
 
 int halo_kernel_max_coresident_blocks(int device) {
     int per_sm = 0, per_sm_ll = 0, sms = 0;
-    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, igg_halo_exchange_kernel, kThreads, 0) != cudaSuccess) return -1;
-    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm_ll, igg_halo_exchange_ll128_kernel, kThreads, 0) != cudaSuccess) return -1;
+    // the fence kernel may be launched with the bulk-copy stages as dynamic shared memory
+    if (cudaFuncSetAttribute(igg_halo_exchange_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kBulkStages * kBulkStageBytes) != cudaSuccess) return -1;
+    if (cudaFuncSetAttribute(igg_halo_exchange_ll128_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kBulkStages * kBulkStageBytes) != cudaSuccess) return -1;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, igg_halo_exchange_kernel, kThreads, kBulkStages * kBulkStageBytes) != cudaSuccess) return -1;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm_ll, igg_halo_exchange_ll128_kernel, kThreads, kBulkStages * kBulkStageBytes) != cudaSuccess) return -1;
     if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device) != cudaSuccess) return -1;
     return (per_sm < per_sm_ll ? per_sm : per_sm_ll) * sms;      // a grid that is co-resident for either kernel
 }
@@ -557,7 +685,7 @@ int launch_halo_kernel(const KParams& p, int grid, void* stream, bool ll128) {
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)grid);
     cfg.blockDim = dim3(kThreads);
-    cfg.dynamicSmemBytes = 0;
+    cfg.dynamicSmemBytes = p.bulk ? kBulkStages * kBulkStageBytes : 0;
     cfg.stream = static_cast<cudaStream_t>(stream);
     cudaLaunchAttribute attr[1];
     attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;

@@ -27,7 +27,8 @@ struct alignas(16) TileRec {
     uint8_t  vec_log2;                          // 0..4
     uint8_t  kind;                              // igg_op_kind
     uint8_t  nbr;                               // neighbour offset index 0..26 (PUSH: target, UNPACK: source)
-    uint8_t  pad[3];
+    uint8_t  bulk;                              // 1: large contiguous rows -- may go through the bulk-copy (TMA) pipeline
+    uint8_t  pad[2];
     uint32_t flag_idx;                          // PUSH: arrival flag to set at the receiver; UNPACK: flag to wait for
     uint32_t pad2;
 };
@@ -38,6 +39,10 @@ constexpr int kThreads      = 256;      // threads per block of the halo kernel 
 constexpr int kBlocksPerSM  = 1024 / kThreads;  // launch bound: 1024 resident threads per SM at <= 64 registers
 constexpr int kTileBytes    = 8192;     // bytes moved per LOCAL / COPY tile (bulk PUSH / UNPACK tiles: Plan::tile_bytes)
 constexpr int kMaxBulkTileBytes = 131072;
+// Bulk-copy pipeline of the fence kernel (halo_kernel.cu): tiles of at least kBulkMinTileBytes whose rows are at least
+// kBulkMinRowBytes long and 16-byte aligned are moved global -> shared -> global by cp.async.bulk through a ring of
+// kBulkStages shared-memory stages of kBulkStageBytes, driven by one thread of the block.
+constexpr int kBulkStageBytes = 16384, kBulkStages = 3, kBulkMinTileBytes = 16384, kBulkMinRowBytes = 1024;
 constexpr size_t kFlagsOff   = 4096;    // control segment: arrival flags start here, one 8-byte word per tile
 constexpr int kMaxFlags      = 1 << 17; // 131 072 tiles per call (about 1 GiB of halo data)
 constexpr size_t kCtrlBytes  = kFlagsOff + (size_t)kMaxFlags * 8;
@@ -100,6 +105,7 @@ struct KParams {
     // Tiles [wx_first, wx_first + wx_count) are kOpWrapX tiles the kernel derives from `wx` below instead of loading
     // them from the table: the strided x-face loads -- the longest latency chain of a call -- start a memory round
     // trip earlier, and a tile-record fetch cannot queue behind the flood of strided loads (wx_count = 0: off).
+    int32_t  bulk;                             // the launch has kBulkStages * kBulkStageBytes of dynamic shared memory
     int32_t  wx_first, wx_count, n_wx_ops;
     WrapXOp  wx[kMaxWxOps];
     char*       copy_dst[2];                   // kOpCopy tiles: destination buffer t.nbr (gather!, NCCL pack)
@@ -129,6 +135,8 @@ struct Plan {
     int32_t  tile_bytes = kTileBytes;                // bytes per PUSH / UNPACK tile of the fence protocol (per plan)
     int64_t  remote_bytes = 0;                       // payload bytes of all staging slots (the same on every rank)
     bool     global_active = false;                  // some rank exchanges with another rank in this call (rank-independent)
+    bool     has_bulk = false;                       // some tile is flagged for the bulk-copy pipeline
+    int64_t  local_bytes = 0;                        // bytes of all self-wrap boxes of this rank
     int32_t  n_push_tiles = 0;
     uint32_t n_flags = 0;                           // arrival flags this plan uses (must be <= kMaxFlags)
     uint32_t active_mask = 0;                        // bit o set: this plan exchanges with the neighbour at offset o

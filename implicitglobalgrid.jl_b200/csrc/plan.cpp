@@ -202,6 +202,10 @@ Lowered emit_tiles(int64_t el, const int64_t ext[3], int64_t src_off, int64_t s_
     int64_t S, R;
     if (V >= per_tile) { S = per_tile; R = 1; } else { S = V; R = std::max<int64_t>(1, per_tile / V); }
     const int64_t segs = (V + S - 1) / S, rblocks = (rows + R - 1) / R;
+    // Tiles with long 16-byte-aligned rows may go through the bulk-copy pipeline (IGG_BULK=0: never).
+    static const bool bulk_on = !(getenv("IGG_BULK") && atoi(getenv("IGG_BULK")) == 0);
+    const bool bulk = bulk_on && v == 16 && tile_bytes >= kBulkMinTileBytes && S * v >= kBulkMinRowBytes &&
+                      (kind == IGG_OP_PUSH || kind == IGG_OP_LOCAL || kind == IGG_OP_UNPACK);
     for (int64_t rb = 0; rb < rblocks; ++rb)
         for (int64_t sg = 0; sg < segs; ++sg) {
             TileRec t;
@@ -217,6 +221,7 @@ Lowered emit_tiles(int64_t el, const int64_t ext[3], int64_t src_off, int64_t s_
             t.vec_log2 = (uint8_t)vlog;
             t.kind = (uint8_t)kind;
             t.nbr = (uint8_t)nbr;
+            t.bulk = (uint8_t)((bulk && (int64_t)t.nrows * t.ncols * v >= kBulkMinTileBytes / 2) ? 1 : 0);
             tiles.push_back(t);
         }
     return Lowered{src_off, dst_off, s_sy, s_sz, d_sy, d_sz, row, ny, nz, v, segs * rblocks, row * rows};
@@ -253,7 +258,7 @@ void lower_op(const igg_field& f, int field_idx, int kind, int nbr, const Box& s
 int64_t auto_bulk_threshold() {
     static const int64_t v = [] {
         const char* e = getenv("IGG_BULK_THRESHOLD");
-        return (e && *e) ? (int64_t)atoll(e) : (int64_t)8 << 20;
+        return (e && *e) ? (int64_t)atoll(e) : (int64_t)64 << 20;
     }();
     return v;
 }
@@ -306,6 +311,7 @@ int build_plan(const igg_grid_desc& g, int nfields, const igg_field* fields, int
     std::vector<int64_t> slot_off((size_t)IGG_NOFFSETS * nfields, -1);
     std::vector<int64_t> slot_n((size_t)IGG_NOFFSETS * nfields, 0);
     plan.remote_bytes = 0;
+    plan.local_bytes = 0;
     for (int oi = 0; oi < IGG_NOFFSETS; ++oi) {
         int o[3];
         index_offset(oi, o);
@@ -317,6 +323,7 @@ int build_plan(const igg_grid_desc& g, int nfields, const igg_field* fields, int
                 if (o[d]) { ok = ok && halo[i][d]; remote = remote || g.dims[d] > 1; n *= fields[i].halowidths[d]; }
                 else n *= fields[i].size[d];
             }
+            if (ok && !remote) plan.local_bytes += n;         // (an upper bound: self-wraps of periodic one-rank dimensions)
             if (!ok || !remote) continue;       // self-wraps copy inside the array and need no staging slot
             slot_n[(size_t)oi * nfields + i] = n;
             plan.remote_bytes += n;
@@ -329,6 +336,10 @@ int build_plan(const igg_grid_desc& g, int nfields, const igg_field* fields, int
     int64_t tb = kTileBytes;
     while (tb < kMaxBulkTileBytes && plan.remote_bytes / tb > 256) tb *= 2;
     plan.tile_bytes = (int32_t)tb;
+    // Self-wraps: 8-KiB tiles (the latency regime's tuning) until a call wraps more than 8 MiB, then growing alike.
+    int64_t tbl = kTileBytes;
+    if (plan.local_bytes > ((int64_t)8 << 20))
+        while (tbl < kMaxBulkTileBytes && plan.local_bytes / tbl > 512) tbl *= 2;
     // Arrival flags: one per tile.  A slot reserves an upper bound of the tiles any box that fits it can have
     // (every full tile covers more than kTileBytes/2 bytes), so that flag numbers too are identical on every rank.
     std::vector<uint32_t> slot_flag((size_t)IGG_NOFFSETS * nfields, 0), slot_nflag((size_t)IGG_NOFFSETS * nfields, 0);
@@ -495,7 +506,7 @@ int build_plan(const igg_grid_desc& g, int nfields, const igg_field* fields, int
                         }
                     }
                 } else {
-                    lower_op(f, i, IGG_OP_LOCAL, oi, snd, rcv_peer, true, true, 0, op, tlocal);
+                    lower_op(f, i, IGG_OP_LOCAL, oi, snd, rcv_peer, true, true, 0, op, tlocal, tbl);
                 }
                 local.push_back(op);
                 plan.bytes_sent += op.nbytes;
@@ -590,6 +601,8 @@ int build_plan(const igg_grid_desc& g, int nfields, const igg_field* fields, int
     plan.wx_count = (int32_t)twrapx.size();
     plan.tiles.insert(plan.tiles.end(), twrapx.begin(), twrapx.end());
     plan.tiles.insert(plan.tiles.end(), tunpack.begin(), tunpack.end());
+    plan.has_bulk = false;           // the LL128 kernel only takes the LOCAL ones through the pipeline
+    for (const TileRec& t : plan.tiles) plan.has_bulk = plan.has_bulk || (t.bulk && (!ll128 || t.kind == IGG_OP_LOCAL));
     return IGG_OK;
 }
 

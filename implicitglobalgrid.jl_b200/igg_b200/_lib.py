@@ -169,7 +169,7 @@ class TileRec(C.Structure):
     _fields_ = [("src_off", C.c_int64), ("dst_off", C.c_int64), ("src_sy", C.c_int64), ("src_sz", C.c_int64),
                 ("dst_sy", C.c_int64), ("dst_sz", C.c_int64), ("row0", C.c_uint32), ("nrows", C.c_uint32),
                 ("ncols", C.c_uint32), ("ny", C.c_uint32), ("field", C.c_uint16), ("vec_log2", C.c_uint8),
-                ("kind", C.c_uint8), ("nbr", C.c_uint8), ("pad", C.c_uint8 * 3), ("flag_idx", C.c_uint32),
+                ("kind", C.c_uint8), ("nbr", C.c_uint8), ("bulk", C.c_uint8), ("pad", C.c_uint8 * 2), ("flag_idx", C.c_uint32),
                 ("pad2", C.c_uint32)]
 
 

@@ -354,7 +354,7 @@ def update_halo(*A, dims=(3, 1, 2), stream=None, blocking=True):
 def set_exchange_mode(mode):
     """Selects how update_halo moves data between ranks.  "ipc": the mode new contexts start in (one fused kernel, peer
     stores over NVLink; "auto" unless the environment variable IGG_MODE names another).  "auto": per call, "ll128"
-    below IGG_BULK_THRESHOLD staged bytes (default 8 MiB), "fence" above.  "ll128": every 128-byte line of staged data
+    below IGG_BULK_THRESHOLD staged bytes (default 64 MiB), "fence" above.  "ll128": every 128-byte line of staged data
     carries its own arrival flag, so there is no release fence and no separate flag (latency regime).  "fence":
     16-byte accesses, one release fence and one arrival flag per tile of 8-128 KiB (bandwidth regime).  "nccl":
     comparison path (per-dimension pack kernel, grouped ncclSend/ncclRecv, unpack kernel).  Every rank must select

@@ -30,9 +30,11 @@ ap.add_argument("--steps", type=int, default=400)
 ap.add_argument("--only", default="")
 ap.add_argument("--modes", default="ipc,nccl", help="comma list of ipc (= the default, auto), auto, ll128, fence, nccl")
 ap.add_argument("--dims", default="", help="dimx,dimy,dimz to force a process grid (e.g. 1,1,2: the z-faces cross NVLink)")
+ap.add_argument("--updims", default="", help="dims= of the update_halo calls, e.g. 3 or 3,2 (default: all)")
 ap.add_argument("--nvl", type=float, default=770.0, help="NVLink GB/s per direction used for the roofline")
 args = ap.parse_args()
 MODES = tuple(m for m in args.modes.split(",") if m)
+UPDIMS = tuple(int(x) for x in args.updims.split(",")) if args.updims else (3, 1, 2)
 FORCED = dict(zip(("dimx", "dimy", "dimz"), (int(x) for x in args.dims.split(",")))) if args.dims else {}
 
 world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -106,12 +108,26 @@ def time_update(name, gsz, kw, shapes, dtype, hws=None, ring_bytes=3.3e9, modes=
             fs.append(t)
         ring.append(fs)
     B, Bn = halo_bytes(g, shapes, hws_, el)
+    if args.updims:          # only the updated dimensions count
+        B = Bn = 0
+        for shp, hw in zip(shapes, hws_):
+            s3 = tuple(shp) + (1,) * (3 - len(shp))
+            for d in [x - 1 for x in UPDIMS]:
+                face = hw[d] * el
+                for k in range(3):
+                    if k != d:
+                        face *= s3[k]
+                for nn in range(2):
+                    nb = g.neighbors[nn][d]
+                    if nb >= 0:
+                        B += face
+                        Bn += face if nb != g.me else 0
     stream = torch.cuda.Stream()
     for mode in modes:
         if mode == "nccl" and world == 1:
             continue
         igg.set_exchange_mode(mode)
-        calls = [igg.prepare_update_halo(*[(t, hw) for t, hw in zip(fs, hws_)], stream=stream, blocking=False) for fs in ring]
+        calls = [igg.prepare_update_halo(*[(t, hw) for t, hw in zip(fs, hws_)], dims=UPDIMS, stream=stream, blocking=False) for fs in ring]
         with torch.cuda.stream(stream):
             for i in range(20):
                 calls[i % nring]()
@@ -137,7 +153,7 @@ def time_update(name, gsz, kw, shapes, dtype, hws=None, ring_bytes=3.3e9, modes=
         barrier()
         us = maxr(e0.elapsed_time(e1)) * 1e3 / K
         t_roof = max(Bn / (NVL * 1e3), 2 * B / (HBM * 1e3)) if B else 0.0      # us
-        rec = {"config": name, "n_gpus": world, "dims": list(g.dims), "mode": mode, "fields": len(shapes),
+        rec = {"config": name + (f" dims={UPDIMS}" if args.updims else ""), "n_gpus": world, "dims": list(g.dims), "mode": mode, "fields": len(shapes),
                "update_halo_us": round(us, 2), "halo_bytes_per_gpu": B, "nvlink_bytes_per_gpu": Bn,
                "halo_GBps_per_gpu": round(B / us / 1e3, 1) if us else None, "roofline_us": round(t_roof, 2),
                "roofline_frac": round(t_roof / us, 3) if us else None,

@@ -262,6 +262,31 @@ def main():
     igg.finalize_global_grid()
     dist.barrier()
 
+    # All ranks in a row along z, four full-size fields (one staggered in x: its rows are not 16-byte aligned): the
+    # contiguous z-faces cross NVLink -- in the fence protocol through the bulk-copy pipeline (tiles of 16 KiB and
+    # more) -- while x and y wrap inside each rank.  Fused path vs NCCL path (checked against the oracle above).
+    # (x halo of two cells = 16 bytes, so that the z-face boxes, which leave the x halo out, keep 16-byte alignment.)
+    igg.init_global_grid(N, N, N, dimx=1, dimy=1, dimz=n, periodx=1, periody=1, periodz=1, overlaps=(4, 2, 2),
+                         halowidths=(2, 1, 1), quiet=True)
+    shapes4 = [(N, N, N), (N, N, N), (N + 1, N, N), (N, N, N)]
+    fa = [igg.zeros(s_, dtype=torch.int64) for s_ in shapes4]
+    for t in fa:
+        t.copy_(torch.randint(-2**62, 2**62, tuple(t.shape), dtype=torch.int64, device="cuda", generator=gen))
+    fb = [t.clone(memory_format=torch.preserve_format) for t in fa]
+    igg.update_halo(*fa, blocking=False)
+    igg.update_halo(*fa)                          # twice: both staging halves, halos must not change
+    igg.set_exchange_mode("nccl")
+    igg.update_halo(*fb)
+    igg.set_exchange_mode(IPC_MODE)
+    torch.cuda.synchronize()
+    for i, (x, y) in enumerate(zip(fa, fb)):
+        if not torch.equal(x, y):
+            ok = False
+            print(f"FULL-SIZE z-row fused/NCCL MISMATCH rank {me} field {i}: {int((x != y).sum())} cells", flush=True)
+    del fa, fb
+    igg.finalize_global_grid()
+    dist.barrier()
+
     # BASELINE config 1 on several ranks: the diffusion3D example, fused CUDA step + update_halo!, bit for bit
     from igg_b200.diffusion3d import Diffusion3D
     from oracle import diffusion_oracle as D

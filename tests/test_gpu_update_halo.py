@@ -491,3 +491,36 @@ def test_blocking_call_completion_paths(blocking_env, monkeypatch):
         for t, w in zip(got, want):
             assert bits_equal(t, w), rep
     igg.finalize_global_grid()
+
+
+@pytest.mark.parametrize("mode", ["fence", "auto"])
+def test_big_self_wraps_bulk_copy_pipeline(mode, monkeypatch):
+    """More than 8 MiB of self-wraps in one call: the LOCAL tiles grow beyond 8 KiB and, in the fence kernel, tiles of
+    long 16-byte-aligned rows go through the cp.async.bulk pipeline (global -> shared -> global); rows that are not
+    16-byte aligned (the field staggered in x: odd row length) and the strided x-faces stay on the load/store path.
+    (x halo of two 8-byte cells: the y/z face boxes, which leave the x halo out, start on 16-byte boundaries.)  Same
+    bits as the oracle either way, twice in a row, blocking and stream-ordered."""
+    monkeypatch.setenv("IGG_MODE", mode)
+    n = (384, 160, 96)
+    kw = dict(periodx=1, periody=1, periodz=1, overlaps=(4, 2, 2), halowidths=(2, 1, 1))
+    igg.init_global_grid(*n, quiet=True, **kw)
+    (g,) = O.make_grids(1, *n, **kw)
+    shapes = [n, n, (n[0] + 1, n[1], n[2]), n, (n[0], n[1] + 1, n[2]), n, n]
+    base = [O.random_bits_field(s, 8, 300 + i) for i, s in enumerate(shapes)]
+    want = [a.copy(order="F") for a in base]
+    O.update_halo([g], [want])
+    ts = [igg.from_numpy(a) for a in base]
+    for rep in range(2):
+        for t, a in zip(ts, base):
+            t.copy_(igg.from_numpy(a))
+        torch.cuda.synchronize()
+        igg.update_halo(*ts, blocking=(rep == 0))
+        torch.cuda.synchronize()
+        for i, (t, w) in enumerate(zip(ts, want)):
+            assert bits_equal(t, w), (mode, rep, i)
+    if mode == "fence":
+        from igg_b200 import _lib as L
+        gg = igg.global_grid()
+        tiles, _ = L.plan_tiles(gg.desc, [L.make_field(t.data_ptr(), tuple(t.shape), gg.halowidths, 8) for t in ts], (3, 1, 2), L.IGG_MODE_IPC_1PHASE)
+        assert any(t.bulk for t in tiles) and any(not t.bulk for t in tiles)
+    igg.finalize_global_grid()

@@ -153,7 +153,7 @@ def test_fence_tiles_grow_with_the_call():
     assert 8192 < max((t.nrows * t.ncols) << t.vec_log2 for t in tiles if t.kind == PUSH) <= 16384
     few, _ = L.plan_tiles(desc_of(grids[0]), cf[:1], (3, 1, 2), L.IGG_MODE_IPC_1PHASE)
     assert max((t.nrows * t.ncols) << t.vec_log2 for t in few if t.kind == PUSH) <= 8192
-    # the default mode picks LL128 for this call (3 MiB staged, below the 8 MiB threshold)
+    # the default mode picks LL128 for this call (3 MiB staged, below the 64 MiB threshold)
     auto, _ = L.plan_tiles(desc_of(grids[0]), cf, (3, 1, 2), L.IGG_MODE_IPC_AUTO)
     assert any(t.kind == PUSH_LL for t in auto) and not any(t.kind == PUSH for t in auto)
 
