@@ -117,6 +117,12 @@ struct igg_ctx {
     // two equivalent kernels for an x self-wrap, never a wrong address.
     struct PtrEntry { const void* user = nullptr; bool host = false; };
     PtrEntry ptr_cache[64];
+    // Symmetric field allocations (igg_alloc_field): the k-th one is "the same array" on every rank, mapped into every
+    // rank's address space, so that a neighbour can store into its copy of a field directly (direct-to-halo).
+    struct FieldReg { char* base = nullptr; int64_t bytes = 0; std::vector<PeerSeg> peer; };   // peer[r]: rank r's copy, mapped here
+    std::vector<FieldReg> regs;                 // index = slot (the same on every rank: allocation is collective)
+    char** d_reg_table = nullptr;               // device: [kMaxFieldRegs][nprocs] base addresses
+    bool direct_enabled = true;                 // IGG_DIRECT=0: never store into a neighbour's field
     // gather
     char* gather_buf = nullptr;   int64_t gather_bytes = 0;       // root: device image of A_global (peer mapped)
     char* gather_src = nullptr;   int64_t gather_src_bytes = 0;   // staging for host-resident A
@@ -135,6 +141,7 @@ struct igg_prepared {
     igg_field fields[IGG_MAX_FIELDS];           // pointers resolved to device addresses
     igg_field user_fields[IGG_MAX_FIELDS];      // as passed in (for the NCCL comparison path)
     uint8_t host_lines[IGG_MAX_FIELDS];
+    uint8_t direct[IGG_MAX_FIELDS];
     int dims_mask = 7;
     int dims_order[3] = {3, 1, 2};
     int ndims_order = 3;
@@ -226,10 +233,13 @@ static void fill_plan_dev(const igg_ctx* ctx, const Plan& plan, PlanDev& d) {
     std::memset(&d, 0, sizeof(d));
     const int pr = plan.ll128 ? 1 : 0;
     d.active_mask = plan.active_mask;
+    d.direct_mask = plan.direct_mask;
     d.unpack_half = ctx->staging_half;
     for (int oi = 0; oi < IGG_NOFFSETS; ++oi) {
         if (!((plan.active_mask >> oi) & 1u)) continue;
         const Peer& peer = ctx->peers[plan.peer[oi]];
+        d.peer_rank[oi] = plan.peer[oi];
+        d.remote_ready[oi] = reinterpret_cast<unsigned long long*>(peer.ctrl.ptr + kReadyOff) + opposite_index(oi);
         // The tiles carry offsets / flag numbers of the plan's own packed layout; shift every offset's base to that
         // offset's region (same table on every rank).  What I push at offset oi lands in the receiver's region of
         // the opposite offset.
@@ -298,7 +308,7 @@ static int ensure_layout(igg_ctx* ctx, const Plan& plan) {
         rc = ctx->cp.barrier();
         if (rc) return rc;
         // An LL128 region may now lie where another protocol's payload was: no stale word may look like an epoch.
-        CU(cudaMemset(ctx->staging, 0, (size_t)(2 * ctx->staging_half)));
+        if (ctx->staging) CU(cudaMemset(ctx->staging, 0, (size_t)(2 * ctx->staging_half)));
         CU(cudaDeviceSynchronize());
         rc = ctx->cp.barrier();
         if (rc) return rc;
@@ -344,8 +354,18 @@ static int proto_of_mode(int mode) {
     return mode == IGG_MODE_IPC_LL128 ? kProtoLL128 : mode == IGG_MODE_IPC_AUTO ? kProtoAuto : kProtoFence;
 }
 
+// Which symmetric allocation (igg_alloc_field) a device address lies in: slot index or -1; *off = offset inside it.
+static int find_reg(const igg_ctx* ctx, const void* p, long long* off) {
+    const char* c = static_cast<const char*>(p);
+    for (size_t k = 0; k < ctx->regs.size(); ++k) {
+        const igg_ctx::FieldReg& r = ctx->regs[k];
+        if (r.base && c >= r.base && c < r.base + r.bytes) { if (off) *off = c - r.base; return (int)k; }
+    }
+    return -1;
+}
+
 static Plan* find_or_build_plan(igg_ctx* ctx, int nfields, const igg_field* fields, int dims_mask, const uint8_t* host_lines,
-                                int* rc_out) {
+                                int* rc_out, const uint8_t* direct = nullptr) {
     const int proto = proto_of_mode(ctx->mode);
     for (auto& up : ctx->plans) {
         Plan* p = up.get();
@@ -355,13 +375,13 @@ static Plan* find_or_build_plan(igg_ctx* ctx, int nfields, const igg_field* fiel
             const FieldKey& k = p->key[i];
             const igg_field& f = fields[i];
             same = k.elsize == f.elsize && k.ndims == f.ndims && k.align == (int32_t)((uintptr_t)f.ptr % 16) &&
-                   k.lines == ((host_lines && host_lines[i]) ? 1 : 0);
+                   k.lines == (((host_lines && host_lines[i]) ? 1 : 0) | ((direct && direct[i]) ? 2 : 0));
             for (int d = 0; d < 3 && same; ++d) same = k.size[d] == f.size[d] && k.hw[d] == f.halowidths[d];
         }
         if (same) { *rc_out = IGG_OK; return p; }
     }
     std::unique_ptr<Plan> plan(new Plan());
-    int rc = build_plan(ctx->g, nfields, fields, dims_mask, *plan, host_lines, proto);
+    int rc = build_plan(ctx->g, nfields, fields, dims_mask, *plan, host_lines, proto, direct);
     if (rc) { *rc_out = rc; return nullptr; }
     plan->proto_req = proto;
     {
@@ -550,6 +570,7 @@ int igg_create(const igg_grid_desc* desc, igg_ctx** out) {
     if (ctx->max_blocks <= 0) return fail(IGG_ERR_CUDA, "occupancy query for the halo kernel failed (was the library built for sm_100a?): %s", cudaGetErrorString(cudaGetLastError()));
     if (const char* t = getenv("IGG_DEVICE_TIMEOUT_S")) ctx->timeout_ns = (unsigned long long)(atof(t) * 1e9);
     if (const char* b = getenv("IGG_BLOCKING")) ctx->spin_wait = strcmp(b, "sync") != 0;
+    if (const char* dd = getenv("IGG_DIRECT")) ctx->direct_enabled = dd[0] != '0';
     // IGG_MODE=fence / ll128 / auto: the IPC protocol a new context starts in (default auto; the same on every rank).
     if (const char* m = getenv("IGG_MODE")) {
         if (!strcmp(m, "ll128")) ctx->mode = IGG_MODE_IPC_LL128;
@@ -579,6 +600,10 @@ int igg_destroy(igg_ctx* ctx) {
     ctx->nccl = nullptr;
     for (auto& p : ctx->peers) { close_segment(p.ctrl); close_segment(p.staging); close_segment(p.gather); }
     for (auto& pl : ctx->plans) { cudaFree(pl->d_plan); cudaFree(pl->d_wrap_tiles); }
+    for (auto& reg : ctx->regs) { for (auto& ps : reg.peer) close_segment(ps); }
+    if (ctx->g.nprocs > 1 && ctx->cp.attached() && !ctx->regs.empty()) ctx->cp.barrier();   // mappings closed before the frees
+    for (auto& reg : ctx->regs) if (reg.base) cudaFree(reg.base);
+    if (ctx->d_reg_table) cudaFree(ctx->d_reg_table);
     if (ctx->staging) cudaFree(ctx->staging);
     if (ctx->gather_buf) cudaFree(ctx->gather_buf);
     if (ctx->gather_src) cudaFree(ctx->gather_src);
@@ -653,6 +678,103 @@ int igg_set_mode(igg_ctx* ctx, int mode) {
     return IGG_OK;
 }
 
+static int upload_reg_table(igg_ctx* ctx) {
+    const int n = ctx->g.nprocs;
+    std::vector<char*> host((size_t)kMaxFieldRegs * n, nullptr);
+    for (size_t k = 0; k < ctx->regs.size(); ++k)
+        for (int r = 0; r < n; ++r)
+            host[k * n + r] = r == ctx->g.me ? ctx->regs[k].base : (ctx->regs[k].base ? ctx->regs[k].peer[r].ptr : nullptr);
+    if (!ctx->d_reg_table) CU(cudaMalloc(&ctx->d_reg_table, host.size() * sizeof(char*)));
+    const cudaError_t e = upload_now(ctx->d_reg_table, host.data(), host.size() * sizeof(char*));
+    if (e != cudaSuccess) return fail(IGG_ERR_CUDA, "field table upload failed: %s", cudaGetErrorString(e));
+    return IGG_OK;
+}
+
+// Symmetric allocation: collective, every rank asks for the same `bytes` in the same order.  cudaMalloc + one CUDA-IPC
+// handle per rank, exchanged through the mailbox; every rank maps every other rank's copy.
+int igg_alloc_field(igg_ctx* ctx, size_t bytes, void** ptr_out) {
+    if (!ctx || !ptr_out || bytes == 0) return fail(IGG_ERR_ARG, "igg_alloc_field: invalid argument.");
+    if (!ctx->bootstrapped) return fail(IGG_ERR_STATE, "igg_alloc_field: call igg_bootstrap_import first (nprocs > 1).");
+    int rc = make_current(ctx);
+    if (rc) return rc;
+    const int n = ctx->g.nprocs, me = ctx->g.me;
+    size_t slot = 0;
+    while (slot < ctx->regs.size() && ctx->regs[slot].base) ++slot;       // first free slot: the same on every rank
+    if (slot >= (size_t)kMaxFieldRegs) return fail(IGG_ERR_ARG, "igg_alloc_field: at most %d symmetric allocations per context.", kMaxFieldRegs);
+    if (slot == ctx->regs.size()) ctx->regs.emplace_back();
+    igg_ctx::FieldReg& reg = ctx->regs[slot];
+    char* mem = nullptr;
+    cudaError_t e = cudaMalloc(&mem, bytes);
+    int status = 0;
+    if (e == cudaSuccess) e = cudaMemset(mem, 0, bytes);
+    if (e == cudaSuccess) e = cudaDeviceSynchronize();
+    if (e != cudaSuccess) { cudaGetLastError(); status = IGG_ERR_CUDA; }
+    reg.peer.assign(n, PeerSeg());
+    if (n > 1) {
+        SegPayload mine;
+        std::memset(&mine, 0, sizeof(mine));
+        mine.proc_nonce = process_nonce();
+        mine.device = ctx->device;
+        mine.status = status;
+        mine.bytes = (int64_t)bytes;
+        mine.ptr = reinterpret_cast<uint64_t>(mem);
+        if (!status && cudaIpcGetMemHandle(&mine.handle, mem) != cudaSuccess) { cudaGetLastError(); mine.status = status = IGG_ERR_IPC; }
+        std::vector<char> all;
+        rc = ctx->cp.allgather(&mine, all);
+        if (rc) { if (mem) cudaFree(mem); return rc; }
+        bool bad = false, differ = false;
+        std::vector<SegPayload> pay(n);
+        std::memcpy(pay.data(), all.data(), all.size());
+        for (int r = 0; r < n; ++r) { bad = bad || pay[r].status != 0; differ = differ || pay[r].bytes != (int64_t)bytes; }
+        for (int r = 0; r < n && !bad && !differ; ++r) {
+            if (r == me) continue;
+            rc = open_segment(ctx, ctx->peers[r], pay[r].handle, pay[r].ptr, reg.peer[r]);
+            if (rc) bad = true;
+            reg.peer[r].bytes = pay[r].bytes;
+        }
+        // everyone learns whether everyone could map everything (a half-registered allocation must not be used)
+        SegPayload verdict;
+        std::memset(&verdict, 0, sizeof(verdict));
+        verdict.status = (bad || differ) ? 1 : 0;
+        rc = ctx->cp.allgather(&verdict, all);
+        if (rc) return rc;
+        std::memcpy(pay.data(), all.data(), all.size());
+        for (int r = 0; r < n; ++r) bad = bad || pay[r].status != 0;
+        if (bad || differ) {
+            for (auto& ps : reg.peer) close_segment(ps);
+            ctx->cp.barrier();
+            if (mem) cudaFree(mem);
+            return fail(differ ? IGG_ERR_ARG : IGG_ERR_IPC, differ ? "igg_alloc_field: the ranks asked for different sizes (the call is collective and symmetric)."
+                                                                   : "igg_alloc_field: allocation or CUDA-IPC mapping failed on some rank.");
+        }
+    } else if (status) {
+        return fail(IGG_ERR_CUDA, "igg_alloc_field: cudaMalloc of %zu bytes failed.", bytes);
+    }
+    reg.base = mem;
+    reg.bytes = (int64_t)bytes;
+    rc = upload_reg_table(ctx);
+    if (rc) return rc;
+    *ptr_out = mem;
+    return IGG_OK;
+}
+
+int igg_free_field(igg_ctx* ctx, void* ptr) {
+    if (!ctx) return fail(IGG_ERR_ARG, "igg_free_field: NULL context.");
+    if (!ptr) return IGG_OK;
+    int rc = make_current(ctx);
+    if (rc) return rc;
+    const int slot = find_reg(ctx, ptr, nullptr);
+    if (slot < 0 || ctx->regs[slot].base != ptr) return fail(IGG_ERR_ARG, "igg_free_field: %p was not returned by igg_alloc_field.", ptr);
+    igg_ctx::FieldReg& reg = ctx->regs[slot];
+    CU(cudaDeviceSynchronize());                    // my kernels are done with everyone's copies ...
+    if (ctx->g.nprocs > 1) { rc = ctx->cp.barrier(); if (rc) return rc; }      // ... and everyone's with mine
+    for (auto& ps : reg.peer) close_segment(ps);
+    if (ctx->g.nprocs > 1) { rc = ctx->cp.barrier(); if (rc) return rc; }      // every mapping of my copy is closed
+    CU(cudaFree(reg.base));
+    reg = igg_ctx::FieldReg();
+    return upload_reg_table(ctx);
+}
+
 }  // extern "C"
 
 // Launches `plan` for `fields` (pointers already resolved).  `sync`: the call is host-synchronous.
@@ -715,6 +837,19 @@ static int launch_plan(igg_ctx* ctx, Plan* plan, int nfields, const igg_field* f
     p.notify_value = 0;
     p.fin_counter = &state->blocks_finished;
     p.bulk = plan->has_bulk ? 1 : 0;
+    p.reg_table = ctx->d_reg_table;
+    p.nprocs = ctx->g.nprocs;
+    p.local_ready = reinterpret_cast<const unsigned long long*>(ctx->ctrl + kReadyOff);
+    for (int i = 0; i < IGG_MAX_FIELDS; ++i) { p.field_reg[i] = -1; p.field_reg_off[i] = 0; }
+    if (plan->direct_mask)
+        for (int i = 0; i < nfields; ++i) {
+            long long off = 0;
+            const int slot = find_reg(ctx, fields[i].ptr, &off);
+            if (slot < 0 && (plan->key[i].lines & 2))
+                return fail(IGG_ERR_STATE, "update_halo: field %d was in a symmetric allocation when the call was planned and is not any more.", i + 1);
+            p.field_reg[i] = (int16_t)slot;
+            p.field_reg_off[i] = off;
+        }
     static const bool wx_params = !(std::getenv("IGG_WX_PARAMS") && std::atoi(std::getenv("IGG_WX_PARAMS")) == 0);
     // (Measured and dropped: letting the WRAPX blocks sleep 400-1200 ns so that the contiguous tiles' loads get out
     // before the strided flood -- 8.62 / 8.76 / 9.01 us against 8.64 us per cfg2 update, cold L2.)
@@ -755,9 +890,9 @@ static int launch_plan(igg_ctx* ctx, Plan* plan, int nfields, const igg_field* f
 
 // The fused single-phase exchange for the dimensions in `dims_mask` (plan lookup, staging growth, one launch).
 static int launch_exchange(igg_ctx* ctx, int nfields, const igg_field* fields, int dims_mask, cudaStream_t stream,
-                           const uint8_t* host_lines, bool sync, bool* waited) {
+                           const uint8_t* host_lines, bool sync, bool* waited, const uint8_t* direct = nullptr) {
     int rc;
-    Plan* plan = find_or_build_plan(ctx, nfields, fields, dims_mask, host_lines, &rc);
+    Plan* plan = find_or_build_plan(ctx, nfields, fields, dims_mask, host_lines, &rc, direct);
     if (!plan) return rc;
     if (!plan->pinned) {
         // A launch recorded into a CUDA graph keeps pointing at the plan's device tables: never evict such a plan.
@@ -768,7 +903,8 @@ static int launch_exchange(igg_ctx* ctx, int nfields, const igg_field* fields, i
     return launch_plan(ctx, plan, nfields, fields, stream, sync, waited);
 }
 
-static int resolve_fields(igg_ctx* ctx, int nfields, const igg_field* fields_in, igg_field* fields, uint8_t* host_lines) {
+static int resolve_fields(igg_ctx* ctx, int nfields, const igg_field* fields_in, igg_field* fields, uint8_t* host_lines,
+                          uint8_t* direct) {
     static const bool host_lines_enabled = !(std::getenv("IGG_HOST_LINES") && std::atoi(std::getenv("IGG_HOST_LINES")) == 0);
     for (int i = 0; i < nfields; ++i) {
         fields[i] = fields_in[i];
@@ -777,6 +913,12 @@ static int resolve_fields(igg_ctx* ctx, int nfields, const igg_field* fields_in,
         if (rc) return rc;
         // Fields in page-locked host memory: whole-line x self-wrap (kOpWrapLines) unless IGG_HOST_LINES=0.
         host_lines[i] = (is_host && host_lines_enabled && (uintptr_t)fields[i].ptr % 64 == 0) ? 1 : 0;
+        // Fields inside a symmetric allocation may be written by the neighbours directly (direct-to-halo).  The whole
+        // array must lie inside the allocation.  (Symmetric: the same verdict on every rank.)
+        long long off = 0;
+        const int slot = (ctx->direct_enabled && ctx->g.nprocs > 1 && !is_host) ? find_reg(ctx, fields[i].ptr, &off) : -1;
+        const long long bytes = (long long)fields[i].size[0] * fields[i].size[1] * fields[i].size[2] * fields[i].elsize;
+        direct[i] = (slot >= 0 && off + bytes <= ctx->regs[slot].bytes) ? 1 : 0;
     }
     return IGG_OK;
 }
@@ -826,14 +968,14 @@ int igg_update_halo(igg_ctx* ctx, int nfields, const igg_field* fields_in, const
     if (rc) return rc;
 
     igg_field fields[IGG_MAX_FIELDS];
-    uint8_t host_lines[IGG_MAX_FIELDS];
-    rc = resolve_fields(ctx, nfields, fields_in, fields, host_lines);
+    uint8_t host_lines[IGG_MAX_FIELDS], direct[IGG_MAX_FIELDS];
+    rc = resolve_fields(ctx, nfields, fields_in, fields, host_lines, direct);
     if (rc) return rc;
 
     const bool sync = !(flags & IGG_ASYNC);
     bool waited = false;
     if (ctx->mode == IGG_MODE_NCCL_3PHASE && ctx->g.nprocs > 1) rc = nccl_update(ctx, nfields, fields, host_lines, dims_order, ndims_order, stream);
-    else rc = launch_exchange(ctx, nfields, fields, dims_mask, stream, host_lines, sync, &waited);
+    else rc = launch_exchange(ctx, nfields, fields, dims_mask, stream, host_lines, sync, &waited, direct);
     if (rc) return rc;
     if (sync && !waited) return wait_done(ctx, stream, 0);
     return IGG_OK;
@@ -855,11 +997,11 @@ int igg_prepare(igg_ctx* ctx, int nfields, const igg_field* fields_in, const int
     h->nfields = nfields;
     if (dims_order && ndims_order > 0) { h->ndims_order = ndims_order; for (int i = 0; i < ndims_order; ++i) h->dims_order[i] = dims_order[i]; }
     for (int i = 0; i < nfields; ++i) h->user_fields[i] = fields_in[i];
-    rc = resolve_fields(ctx, nfields, fields_in, h->fields, h->host_lines);
+    rc = resolve_fields(ctx, nfields, fields_in, h->fields, h->host_lines, h->direct);
     if (rc) return rc;
     // Building the plan here allocates its device tables now, not in the time loop.  (Staging for exchanges between
     // ranks still grows at the first call that needs it: that step is collective.)
-    h->plan = find_or_build_plan(ctx, nfields, h->fields, h->dims_mask, h->host_lines, &rc);
+    h->plan = find_or_build_plan(ctx, nfields, h->fields, h->dims_mask, h->host_lines, &rc, h->direct);
     if (!h->plan) return rc;
     h->plan->pinned = true;
     h->mode = ctx->mode;
@@ -883,7 +1025,7 @@ int igg_update_halo_prepared(igg_prepared* h, void* stream_v, int flags) {
         rc = nccl_update(ctx, h->nfields, h->fields, h->host_lines, h->dims_order, h->ndims_order, stream);
     } else {
         if (h->mode != ctx->mode) {            // the exchange mode changed since: the plan of the new mode
-            h->plan = find_or_build_plan(ctx, h->nfields, h->fields, h->dims_mask, h->host_lines, &rc);
+            h->plan = find_or_build_plan(ctx, h->nfields, h->fields, h->dims_mask, h->host_lines, &rc, h->direct);
             if (!h->plan) return rc;
             h->plan->pinned = true;
             h->mode = ctx->mode;

@@ -464,6 +464,19 @@ __device__ __forceinline__ bool unpack_ll_tile(const TileRec& t, char* __restric
     return true;
 }
 
+// One thread waits until *word >= want (acquire, system scope); a device-side time-out sets the status word.
+__device__ __noinline__ void spin_until(const unsigned long long* word, unsigned long long want, const KParams& p) {
+    unsigned long long t0 = 0;
+    unsigned int spins = 0;
+    while (ld_acquire_sys(word) < want) {
+        if ((++spins & 0x3ff) == 0) {
+            const unsigned long long now = globaltimer_ns();
+            if (t0 == 0) t0 = now;
+            else if (now - t0 > p.timeout_ns) { *reinterpret_cast<volatile int*>(p.status) = IGG_ERR_TIMEOUT; break; }
+        }
+    }
+}
+
 template <bool LL>
 __device__ __forceinline__ void halo_exchange_body(const KParams& p) {
     __shared__ unsigned long long s_epoch;            // flag value of this launch (exchange launches so far + 1)
@@ -505,6 +518,10 @@ __device__ __forceinline__ void halo_exchange_body(const KParams& p) {
         }
         if (threadIdx.x == 32) s_epoch = __ldcg(&p.state->call_epoch) + 1ull;
         __syncthreads();
+        // Direct-to-halo: this launch has started, so every earlier kernel of my stream is done with my halos: tell
+        // the neighbours that will store into them (their PUSH_DIRECT tiles wait for exactly this epoch).
+        if (blockIdx.x == 0 && threadIdx.x < IGG_NOFFSETS && p.plan && ((p.plan->direct_mask >> threadIdx.x) & 1u))
+            st_relaxed_sys(p.plan->remote_ready[threadIdx.x], s_epoch);
     }
     // Every block has now read the state it needs and says so; the last block to have said so advances the state for
     // the next launch (which is stream-ordered after this one) -- after its tiles, below: the count is issued here and
@@ -579,6 +596,13 @@ __device__ __forceinline__ void halo_exchange_body(const KParams& p) {
                 }
                 if (first) IGG_TRACE(3);
             }
+        } else if (t.kind == kOpWait) {
+            // Direct-to-halo, receiver's side: the neighbour stores into my halo itself; only its arrival flag is
+            // waited for (so that the launch does not end before the halo is complete).
+            if (threadIdx.x == 0) {
+                spin_until(p.local_flags + ((long long)t.flag_idx + s_lflag_delta[t.nbr]), s_epoch, p);
+                if (first) IGG_TRACE(5);
+            }
         } else if (!LL && t.kind == IGG_OP_UNPACK) {
             // Wait until the neighbour has flagged this very tile (it flags each tile right after storing it).
             if (threadIdx.x == 0) {
@@ -601,14 +625,22 @@ __device__ __forceinline__ void halo_exchange_body(const KParams& p) {
         } else {
             // PUSH: my field -> peer staging; LOCAL: my field -> my field; COPY (gather!, NCCL pack): field -> buffer;
             // COPY_IN (NCCL unpack): buffer filled by an earlier stream operation -> my field.
+            // PUSH_DIRECT (direct-to-halo): my send box -> the receive box of the NEIGHBOUR's copy of the field, once
+            // the neighbour's launch of this epoch has started (ready word: its halo may be overwritten); released
+            // like a PUSH tile.
             const char* src = (t.kind == kOpCopyIn ? p.copy_src[t.nbr] : static_cast<const char*>(p.field[t.field])) + t.src_off;
             char* dst;
             if (t.kind == IGG_OP_LOCAL || t.kind == kOpCopyIn) dst = static_cast<char*>(p.field[t.field]) + t.dst_off;
             else if (!LL && t.kind == IGG_OP_PUSH) dst = s_push[t.nbr] + t.dst_off;
+            else if (t.kind == kOpPushDirect) {
+                dst = p.reg_table[(long long)p.field_reg[t.field] * p.nprocs + p.plan->peer_rank[t.nbr]] + p.field_reg_off[t.field] + t.dst_off;
+                if (threadIdx.x == 0) spin_until(p.local_ready + t.nbr, s_epoch, p);
+                __syncthreads();
+            }
             else dst = p.copy_dst[t.nbr] + t.dst_off;
             copy_tile_dispatch<false>(t, src, dst);
             if (first) IGG_TRACE(3);
-            if (!LL && t.kind == IGG_OP_PUSH) {
+            if ((!LL && t.kind == IGG_OP_PUSH) || t.kind == kOpPushDirect) {
                 // Release this tile to the neighbour: all stores of the block (ordered before thread 0 by the barrier)
                 // become visible system-wide before the tile's arrival flag does.  Other warps move on to the next tile.
                 __syncthreads();

@@ -67,8 +67,15 @@ struct PlanDev {
     int32_t     local_flag_delta[IGG_NOFFSETS];      // UNPACK tile of offset o waits for local_flags[flag_idx + delta[o]]
     long long   unpack_half;                   // bytes of one staging half of mine
     uint32_t    active_mask;                   // bit o: launches of this plan exchange with the neighbour at offset o
-    uint32_t    pad;
+    uint32_t    direct_mask;                   // bit o: some box goes straight into the field of the neighbour at offset o
+    // Direct-to-halo: where my "launch k has started, my halos may be overwritten" word lives on the neighbour at
+    // offset o (its ready[26 - o]), and which rank that neighbour is (row of the context's field table).
+    unsigned long long* remote_ready[IGG_NOFFSETS];
+    int32_t     peer_rank[IGG_NOFFSETS];
+    int32_t     pad;
 };
+constexpr size_t kReadyOff = 2048;             // control segment: ready[27] words, written by the neighbours
+constexpr int kMaxFieldRegs = 64;              // symmetric field allocations per context (igg_alloc_field)
 
 // One periodic x self-wrap of a field (both x-faces), as the kernel needs it to derive a kOpWrapX tile WITHOUT a
 // tile-table load: tile j of the op covers rows [j * rows_per_tile, ...) (see kOpWrapX below for the geometry).
@@ -106,6 +113,13 @@ struct KParams {
     // them from the table: the strided x-face loads -- the longest latency chain of a call -- start a memory round
     // trip earlier, and a tile-record fetch cannot queue behind the flood of strided loads (wx_count = 0: off).
     int32_t  bulk;                             // the launch has kBulkStages * kBulkStageBytes of dynamic shared memory
+    // Direct-to-halo: field i of the call lives at byte field_reg_off[i] of symmetric allocation field_reg[i] (-1:
+    // not in one); reg_table[field_reg[i] * nprocs + r] is where that allocation is mapped for rank r's copy.
+    char* const* reg_table;
+    int32_t  nprocs;
+    const unsigned long long* local_ready;     // my ready[27] words
+    int16_t  field_reg[IGG_MAX_FIELDS];
+    long long field_reg_off[IGG_MAX_FIELDS];
     int32_t  wx_first, wx_count, n_wx_ops;
     WrapXOp  wx[kMaxWxOps];
     char*       copy_dst[2];                   // kOpCopy tiles: destination buffer t.nbr (gather!, NCCL pack)
@@ -140,6 +154,7 @@ struct Plan {
     int32_t  n_push_tiles = 0;
     uint32_t n_flags = 0;                           // arrival flags this plan uses (must be <= kMaxFlags)
     uint32_t active_mask = 0;                        // bit o set: this plan exchanges with the neighbour at offset o
+    uint32_t direct_mask = 0;                        // bit o set: some box goes straight into that neighbour's field
     int32_t  peer[IGG_NOFFSETS];                     // rank at offset o (or -1)
     int64_t  staging_bytes = 0;                      // bytes of one staging half this plan needs
     // Per neighbour offset o: where this plan's slots / flags of offset o start when the offsets are packed one after
@@ -183,8 +198,9 @@ int ranges(const igg_grid_desc& g, const igg_field& f, int n, int dim, bool send
 // per call, the fence protocol above (decided from numbers that are the same on every rank).
 constexpr int kProtoFence = 0, kProtoLL128 = 1, kProtoAuto = 2;
 int64_t auto_bulk_threshold();
+// `direct[i]` != 0 (optional): field i lives in a symmetric allocation on every rank (direct-to-halo allowed).
 int build_plan(const igg_grid_desc& g, int nfields, const igg_field* fields, int dims_mask, Plan& plan,
-               const uint8_t* host_lines = nullptr, int proto = kProtoFence);
+               const uint8_t* host_lines = nullptr, int proto = kProtoFence, const uint8_t* direct = nullptr);
 void build_block_copy_tiles(int64_t el, const int64_t ext[3], const int64_t dst_size[2], const int64_t dst_origin[3],
                             int64_t src_align, int64_t dst_align, std::vector<TileRec>& tiles);
 constexpr int kOpCopy = 3;   // internal tile kind: field[t.field] -> push_base[t.nbr], no signalling (gather!, NCCL pack)
@@ -217,6 +233,15 @@ constexpr int kOpUnpackLL = 7;
 // src_sy / src_sz = row / plane strides, dst_sy = (ol - hw) * elsize (high send = high halo - dst_sy, low halo =
 // low send - dst_sy), ncols = words per side per row, row0 / nrows / ny as for copy tiles.
 constexpr int kOpWrapX = 8;
+// Direct-to-halo (fields inside symmetric allocations, igg_alloc_field): a send box whose rows span x goes straight
+// into the receive box of the neighbour's copy of the field -- no staging, no unpack.  kOpPushDirect: like PUSH, but
+// dst_off / dst_sy / dst_sz address the NEIGHBOUR's field (same shape as mine); the block first waits until the
+// neighbour's launch of the same epoch has started (ready word: its earlier kernels are done with the halo), and
+// releases the tile like the fence protocol does (barrier, fence.acq_rel.sys, arrival flag).  kOpWait: the
+// receiver's side of such a tile: wait for the arrival flag, copy nothing.
+constexpr int kOpPushDirect = 9;
+constexpr int kOpWait = 10;
+constexpr int64_t kDirectMinRowBytes = 1024;   // direct only for boxes that span x of fields at least this wide
 constexpr int kWrapXRowsPerTile = 256;
 constexpr int kLinePayload = 120;
 constexpr int kLinesPerTile = 64;

@@ -205,7 +205,7 @@ Lowered emit_tiles(int64_t el, const int64_t ext[3], int64_t src_off, int64_t s_
     // Tiles with long 16-byte-aligned rows may go through the bulk-copy pipeline (IGG_BULK=0: never).
     static const bool bulk_on = !(getenv("IGG_BULK") && atoi(getenv("IGG_BULK")) == 0);
     const bool bulk = bulk_on && v == 16 && tile_bytes >= kBulkMinTileBytes && S * v >= kBulkMinRowBytes &&
-                      (kind == IGG_OP_PUSH || kind == IGG_OP_LOCAL || kind == IGG_OP_UNPACK);
+                      (kind == IGG_OP_PUSH || kind == IGG_OP_LOCAL || kind == IGG_OP_UNPACK);       // (not the direct kinds)
     for (int64_t rb = 0; rb < rblocks; ++rb)
         for (int64_t sg = 0; sg < segs; ++sg) {
             TileRec t;
@@ -263,8 +263,21 @@ int64_t auto_bulk_threshold() {
     return v;
 }
 
+// Staged bytes per call from which fields in symmetric allocations are updated direct-to-halo.  Measured on 2 B200s
+// in a row along z (profiles/direct_ab_n2_r02.log): the ready hand-shake and the release fence make it slower than
+// LL128 staging for small calls (cfg2, 1 MiB: 16.0 vs 10.8 us), while from a few MiB on it wins by not unpacking
+// (cfg4 F = 1 / 2 / 4, 4 - 16 MiB: 33.7 / 61.2 / 115.6 vs 35.5 / 71.1 / 143.6 us).  IGG_DIRECT_THRESHOLD overrides it
+// (bytes; the same on every rank).
+static int64_t direct_threshold() {
+    static const int64_t v = [] {
+        const char* e = getenv("IGG_DIRECT_THRESHOLD");
+        return (e && *e) ? (int64_t)atoll(e) : (int64_t)4 << 20;
+    }();
+    return v;
+}
+
 int build_plan(const igg_grid_desc& g, int nfields, const igg_field* fields, int dims_mask, Plan& plan,
-               const uint8_t* host_lines, int proto) {
+               const uint8_t* host_lines, int proto, const uint8_t* direct) {
     int rc = check_grid(g);
     if (rc) return rc;
     rc = check_fields(g, nfields, fields);
@@ -277,7 +290,7 @@ int build_plan(const igg_grid_desc& g, int nfields, const igg_field* fields, int
         for (int d = 0; d < 3; ++d) { k.size[d] = fields[i].size[d]; k.hw[d] = fields[i].halowidths[d]; }
         k.elsize = fields[i].elsize; k.ndims = fields[i].ndims;
         k.align = (int32_t)((uintptr_t)fields[i].ptr % 16);
-        k.lines = (host_lines && host_lines[i]) ? 1 : 0;
+        k.lines = ((host_lines && host_lines[i]) ? 1 : 0) | ((direct && direct[i]) ? 2 : 0);
         plan.key.push_back(k);
     }
     plan.dims_mask = dims_mask;
@@ -286,6 +299,14 @@ int build_plan(const igg_grid_desc& g, int nfields, const igg_field* fields, int
     plan.wrap_tiles.clear();
     plan.wx_ops.clear();
     plan.active_mask = 0;
+    plan.direct_mask = 0;
+    // Direct-to-halo for (offset, field): the field lives in a symmetric allocation and the box spans x with rows of
+    // at least kDirectMinRowBytes -- decided from numbers that are the same on every rank.  Strided x-faces (and the
+    // edges / corners with an x component) stay staged: they would cross NVLink as 8-byte stores.
+    bool direct_on = false;          // set once the call's staged bytes are known (below)
+    auto is_direct = [&](const int o[3], int i) {
+        return direct_on && direct[i] && o[0] == 0 && fields[i].size[0] * (int64_t)fields[i].elsize >= kDirectMinRowBytes;
+    };
     plan.bytes_sent = 0;
 
     bool exists[3][2];
@@ -329,6 +350,7 @@ int build_plan(const igg_grid_desc& g, int nfields, const igg_field* fields, int
             plan.remote_bytes += n;
         }
     }
+    direct_on = direct != nullptr && plan.remote_bytes >= direct_threshold();
     const bool ll128 = proto == kProtoLL128 || (proto == kProtoAuto && plan.remote_bytes < auto_bulk_threshold());
     plan.ll128 = ll128;
     // Fence protocol: tiles grow with the call so that a call has a few hundred PUSH tiles (one release fence each),
@@ -363,6 +385,12 @@ int build_plan(const igg_grid_desc& g, int nfields, const igg_field* fields, int
             const int64_t n = slot_n[(size_t)oi * nfields + i];
             if (n == 0) continue;
             slot_off[(size_t)oi * nfields + i] = total;
+            if (is_direct(o, i)) {              // no staging bytes, only arrival flags (one per tile)
+                slot_flag[(size_t)oi * nfields + i] = nflags;
+                slot_nflag[(size_t)oi * nfields + i] = (uint32_t)(2 * ((n + tb - 1) / tb) + 1);
+                nflags += slot_nflag[(size_t)oi * nfields + i];
+                continue;
+            }
             if (ll128) {                        // lines of 120 payload bytes + 8 flag bytes; no separate flags
                 if (n >= (int64_t)1 << 32)
                     return fail(IGG_ERR_ARG, "update_halo: a halo box of 4 GiB or more is not supported by the LL128 protocol.");
@@ -513,6 +541,45 @@ int build_plan(const igg_grid_desc& g, int nfields, const igg_field* fields, int
             } else {
                 op.kind = IGG_OP_PUSH;
                 op.staging_off = slot_off[(size_t)opposite_index(oi) * nfields + i];
+                if (is_direct(o, i)) {
+                    // Straight into the neighbour's receive box (its copy of the field has my field's shape).  The op
+                    // descriptions say so with staging_off = -1 on both sides; the receiver only waits.
+                    const size_t first = tpush.size();
+                    op.staging_off = -1;
+                    lower_op(f, i, kOpPushDirect, oi, snd, rcv_peer, true, true, 0, op, tpush, tb);
+                    if (tpush.size() - first > slot_nflag[(size_t)opposite_index(oi) * nfields + i])
+                        return fail(IGG_ERR_STATE, "internal: a direct op has more tiles than its slot has arrival flags.");
+                    for (size_t k = first; k < tpush.size(); ++k) {
+                        tpush[k].flag_idx = slot_flag[(size_t)opposite_index(oi) * nfields + i] + (uint32_t)(k - first);
+                        tpush[k].bulk = 0;
+                    }
+                    op.flag_base = (int32_t)slot_flag[(size_t)opposite_index(oi) * nfields + i];
+                    push.push_back(op);
+                    plan.active_mask |= 1u << oi;
+                    plan.direct_mask |= 1u << oi;
+                    plan.bytes_sent += op.nbytes;
+
+                    igg_plan_op up;
+                    std::memset(&up, 0, sizeof(up));
+                    up.kind = IGG_OP_UNPACK;
+                    up.field = i;
+                    up.peer = (int32_t)peer;
+                    for (int d = 0; d < 3; ++d) {
+                        up.offset[d] = o[d];
+                        up.dst_lo[d] = rcv_mine.lo[d]; up.dst_hi[d] = rcv_mine.hi[d];
+                    }
+                    up.staging_off = -1;
+                    const size_t firstw = tunpack.size();
+                    lower_op(f, i, kOpWait, oi, rcv_mine, rcv_mine, true, true, 0, up, tunpack, tb);
+                    for (size_t k = firstw; k < tunpack.size(); ++k) {
+                        tunpack[k].flag_idx = slot_flag[(size_t)oi * nfields + i] + (uint32_t)(k - firstw);
+                        tunpack[k].bulk = 0;
+                    }
+                    up.flag_base = (int32_t)slot_flag[(size_t)oi * nfields + i];
+                    up.nbytes = 0;
+                    unpack.push_back(up);
+                    continue;
+                }
                 if (ll128) {
                     // Same boxes, line-formatted staging: the op descriptions keep the field-side geometry (merged
                     // rows and strides); the tiles are runs of staging lines.
@@ -707,14 +774,19 @@ int igg_plan_tiles(const igg_grid_desc* desc, int nfields, const igg_field* fiel
                    int mode, void* tiles_out, int tiles_cap, int* ntiles_out, int64_t* staging_bytes_out,
                    int64_t* regions_out) {
     if (!desc || !fields || !ntiles_out) return igg::fail(IGG_ERR_ARG, "igg_plan_tiles: NULL argument.");
+    const bool all_direct = (mode & 0x100) != 0;      // + 0x100: every field lives in a symmetric allocation
+    mode &= 0xff;
     if (mode != IGG_MODE_IPC_1PHASE && mode != IGG_MODE_IPC_LL128 && mode != IGG_MODE_IPC_AUTO)
         return igg::fail(IGG_ERR_ARG, "igg_plan_tiles: mode must be an IPC mode.");
+    uint8_t direct[IGG_MAX_FIELDS];
+    std::memset(direct, all_direct ? 1 : 0, sizeof(direct));
     int mask;
     int rc = igg::dims_mask_from_order(dims_order, ndims_order, &mask);
     if (rc) return rc;
     igg::Plan plan;
     rc = igg::build_plan(*desc, nfields, fields, mask, plan, nullptr,
-                         mode == IGG_MODE_IPC_LL128 ? igg::kProtoLL128 : mode == IGG_MODE_IPC_AUTO ? igg::kProtoAuto : igg::kProtoFence);
+                         mode == IGG_MODE_IPC_LL128 ? igg::kProtoLL128 : mode == IGG_MODE_IPC_AUTO ? igg::kProtoAuto : igg::kProtoFence,
+                         direct);
     if (rc) return rc;
     *ntiles_out = (int)plan.tiles.size();
     if (staging_bytes_out) *staging_bytes_out = plan.staging_bytes;

@@ -10,7 +10,7 @@ Importing the package does not load the shared library; the first call that need
 missing (there is no Python/CPU fallback for the data path).
 """
 from ._lib import IGGError, LIB_PATH
-from .api import (ArgumentError, GlobalGrid, finalize_global_grid, from_numpy, gather, get_global_grid, global_grid,
+from .api import (ArgumentError, GlobalGrid, alloc_field, free_field, finalize_global_grid, from_numpy, gather, get_global_grid, global_grid,
                   grid_is_initialized, init_global_grid, ix_g, iy_g, iz_g, nx_g, ny_g, nz_g, prepare_update_halo, set_exchange_mode,
                   select_device, tic, to_numpy,
                   toc, update_halo, x_g, y_g, z_g, zeros)
@@ -23,4 +23,4 @@ gather_ = gather
 __all__ = ["IGGError", "ArgumentError", "GlobalGrid", "LIB_PATH", "init_global_grid", "finalize_global_grid",
            "update_halo", "update_halo_", "prepare_update_halo", "set_exchange_mode", "gather", "gather_", "select_device", "get_global_grid", "global_grid",
            "grid_is_initialized", "nx_g", "ny_g", "nz_g", "x_g", "y_g", "z_g", "ix_g", "iy_g", "iz_g", "tic", "toc",
-           "zeros", "from_numpy", "to_numpy", "CellArray"]
+           "zeros", "alloc_field", "free_field", "from_numpy", "to_numpy", "CellArray"]

@@ -81,6 +81,8 @@ def load():
         "igg_prepare": (C.c_int, [vp, i32, fp, i32p, i32, C.POINTER(vp)]),
         "igg_update_halo_prepared": (C.c_int, [vp, vp, i32]),
         "igg_release_prepared": (C.c_int, [vp]),
+        "igg_alloc_field": (C.c_int, [vp, C.c_size_t, C.POINTER(vp)]),
+        "igg_free_field": (C.c_int, [vp, vp]),
         "igg_update_halo_noalloc": (C.c_int, [gd, i32, fp, i32p, i32, vp, i32]),
         "igg_noalloc_scratch_bytes": (C.c_int64, []),
         "igg_set_mode": (C.c_int, [vp, i32]),
@@ -115,7 +117,7 @@ def load():
 
 DECLARED_SYMBOLS = [
     "igg_version", "igg_last_error", "igg_create", "igg_destroy", "igg_bootstrap_size", "igg_bootstrap_export",
-    "igg_bootstrap_import", "igg_update_halo", "igg_prepare", "igg_update_halo_prepared", "igg_release_prepared", "igg_update_halo_noalloc", "igg_noalloc_scratch_bytes", "igg_set_mode", "igg_nccl_unique_id_size", "igg_nccl_get_unique_id",
+    "igg_bootstrap_import", "igg_update_halo", "igg_prepare", "igg_update_halo_prepared", "igg_release_prepared", "igg_alloc_field", "igg_free_field", "igg_update_halo_noalloc", "igg_noalloc_scratch_bytes", "igg_set_mode", "igg_nccl_unique_id_size", "igg_nccl_get_unique_id",
     "igg_nccl_init", "igg_gather", "igg_diffusion3d_step", "igg_sendranges", "igg_recvranges", "igg_check_fields", "igg_plan_describe", "igg_plan_tiles",
     "igg_ctrl_selftest_create", "igg_ctrl_selftest_run", "igg_debug_state", "igg_debug_issue_loop", "igg_debug_timed_calls", "igg_trace_enable", "igg_trace_read",
     "igg_launch_count", "igg_kernel_name",

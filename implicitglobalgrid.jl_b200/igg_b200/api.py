@@ -194,6 +194,7 @@ def finalize_global_grid(*, finalize_MPI=True):
     global _grid
     check_initialized()
     _call_cache.clear()
+    _sym_fields.clear()          # igg_destroy releases the symmetric allocations
     if _grid.ctx:
         L.check(L.load().igg_destroy(_grid.ctx))
     _grid = None
@@ -210,6 +211,44 @@ def zeros(shape, dtype=None, device=None, pin_memory=False):
         device = "cpu" if pin_memory else f"cuda:{torch.cuda.current_device()}"
     t = torch.zeros(tuple(reversed(shape)), dtype=dtype, device=device, pin_memory=pin_memory)
     return t.permute(*reversed(range(len(shape))))
+
+
+class _DevBlob:
+    """Raw device memory as something torch.as_tensor understands (CUDA array interface)."""
+
+    def __init__(self, ptr, nbytes):
+        self.__cuda_array_interface__ = {"shape": (nbytes,), "typestr": "|u1", "data": (ptr, False), "version": 3}
+
+
+_sym_fields = {}
+
+
+def alloc_field(shape, dtype=None):
+    """A zero-initialised column-major array of Julia size `shape` inside a SYMMETRIC allocation (igg_alloc_field):
+    collective -- every rank calls it with the same shape and dtype in the same order.  update_halo! then stores the
+    y/z faces of such a field straight into the neighbours' halos over NVLink (direct-to-halo) instead of staging
+    and unpacking them.  Release it with free_field (collective) before finalize_global_grid, or let finalize do it."""
+    torch = _torch()
+    g = global_grid()
+    shape = tuple(int(s) for s in (shape if isinstance(shape, (tuple, list)) else (shape,)))
+    dtype = dtype or torch.float64
+    el = torch.empty((), dtype=dtype).element_size()
+    n = 1
+    for s_ in shape:
+        n *= s_
+    ptr = C.c_void_p()
+    L.check(L.load().igg_alloc_field(g.ctx, n * el, C.byref(ptr)))
+    raw = torch.as_tensor(_DevBlob(ptr.value, n * el), device=f"cuda:{torch.cuda.current_device()}")
+    t = raw.view(dtype).reshape(tuple(reversed(shape))).permute(*reversed(range(len(shape))))
+    _sym_fields[t.data_ptr()] = ptr.value
+    return t
+
+
+def free_field(t):
+    """Releases an array made by alloc_field (collective).  The tensor must not be used afterwards."""
+    g = global_grid()
+    ptr = _sym_fields.pop(t.data_ptr())
+    L.check(L.load().igg_free_field(g.ctx, C.c_void_p(ptr)))
 
 
 def from_numpy(a, device=None):

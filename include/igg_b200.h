@@ -143,6 +143,19 @@ int igg_prepare(igg_ctx* ctx, int nfields, const igg_field* fields, const int* d
 int igg_update_halo_prepared(igg_prepared* call, void* stream, int flags);
 int igg_release_prepared(igg_prepared* call);
 
+/* ---- direct-to-halo: fields the neighbours may store into -------------------------------------------------------
+ * igg_alloc_field / igg_free_field replace, for the arrays themselves, what the reference leaves to CUDA.jl
+ * (`CUDA.zeros`, e.g. ref: examples/diffusion3D_multigpu_CuArrays_novis.jl:27-33) -- and make the reference's receive
+ * buffers and unpack step (ref: src/CUDAExt/update_halo.jl:190-203 iread_recvbufs!, :220-227 read_x2d!) unnecessary
+ * for them: an allocation made here is SYMMETRIC (collective: every rank calls with the same size in the same order)
+ * and mapped into every rank's address space through CUDA IPC, so that update_halo! of a field inside it stores every
+ * send box that spans x (the y/z faces and the y-z edges: rows of at least 1 KiB) straight into the neighbour's halo
+ * over NVLink; the strided x-faces and fields in foreign memory keep going through staging.  A field must lie at
+ * the same offset of the same allocation on every rank (e.g. the k-th allocation holds array k everywhere).
+ * Zero-initialised.  IGG_DIRECT=0 in the environment keeps everything staged (for comparison). */
+int igg_alloc_field(igg_ctx* ctx, size_t bytes, void** ptr_out);
+int igg_free_field(igg_ctx* ctx, void* ptr);
+
 /* igg_update_halo_noalloc -- no counterpart in the reference.
  * The same halo update for callers that are not allowed to allocate device memory (a host application whose own pool
  * owns the GPU, a library entered where an allocation would stall the caller's streams, a time loop that guarantees
@@ -224,8 +237,9 @@ int igg_plan_describe(const igg_grid_desc* desc, int nfields, const igg_field* f
                       igg_plan_op* ops_out, int ops_cap, int* nops_out, int64_t* staging_bytes_out);
 /* The tile table the exchange kernel would walk in `mode` (IGG_MODE_IPC_1PHASE or IGG_MODE_IPC_LL128) for this call
  * on this rank: `*ntiles_out` records of 80 bytes each (layout: struct TileRec in csrc/igg_internal.h; PUSH tiles
- * first, then the x self-wraps (WRAPX) and the other LOCAL tiles, then UNPACK).  `mode` may also be
- * IGG_MODE_IPC_AUTO.  `regions_out` (may be NULL) receives 4 x 27 numbers, indexed by neighbour offset
+ * first, then the LOCAL tiles and the x self-wraps (WRAPX), then UNPACK).  `mode` may also be
+ * IGG_MODE_IPC_AUTO; adding 0x100 to it treats every field as living in a symmetric allocation (igg_alloc_field):
+ * boxes that span x then go straight into the neighbour's field (PUSH_DIRECT tiles) and the receiver only waits.  `regions_out` (may be NULL) receives 4 x 27 numbers, indexed by neighbour offset
  * (ox+1) + 3(oy+1) + 9(oz+1): where that offset's staging slots start in the table's packed layout, how many bytes
  * of a staging half the offset needs, and the same two for its arrival flags.  (At run time every offset owns a
  * region whose position does not depend on the call; the launch shifts each offset's base accordingly.)

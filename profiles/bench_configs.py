@@ -31,6 +31,7 @@ ap.add_argument("--only", default="")
 ap.add_argument("--modes", default="ipc,nccl", help="comma list of ipc (= the default, auto), auto, ll128, fence, nccl")
 ap.add_argument("--dims", default="", help="dimx,dimy,dimz to force a process grid (e.g. 1,1,2: the z-faces cross NVLink)")
 ap.add_argument("--updims", default="", help="dims= of the update_halo calls, e.g. 3 or 3,2 (default: all)")
+ap.add_argument("--sym", action="store_true", help="fields in symmetric allocations (igg.alloc_field): direct-to-halo")
 ap.add_argument("--nvl", type=float, default=770.0, help="NVLink GB/s per direction used for the roofline")
 args = ap.parse_args()
 MODES = tuple(m for m in args.modes.split(",") if m)
@@ -103,7 +104,7 @@ def time_update(name, gsz, kw, shapes, dtype, hws=None, ring_bytes=3.3e9, modes=
     for r in range(nring):
         fs = []
         for s in shapes:
-            t = igg.zeros(s, dtype=dtype)
+            t = igg.alloc_field(s, dtype=dtype) if args.sym else igg.zeros(s, dtype=dtype)
             t.copy_(torch.randn(tuple(reversed(s)), device="cuda").to(dtype).permute(*reversed(range(len(s)))))
             fs.append(t)
         ring.append(fs)
@@ -153,7 +154,7 @@ def time_update(name, gsz, kw, shapes, dtype, hws=None, ring_bytes=3.3e9, modes=
         barrier()
         us = maxr(e0.elapsed_time(e1)) * 1e3 / K
         t_roof = max(Bn / (NVL * 1e3), 2 * B / (HBM * 1e3)) if B else 0.0      # us
-        rec = {"config": name + (f" dims={UPDIMS}" if args.updims else ""), "n_gpus": world, "dims": list(g.dims), "mode": mode, "fields": len(shapes),
+        rec = {"config": name + (f" dims={UPDIMS}" if args.updims else "") + (" [symmetric fields]" if args.sym else ""), "n_gpus": world, "dims": list(g.dims), "mode": mode, "fields": len(shapes),
                "update_halo_us": round(us, 2), "halo_bytes_per_gpu": B, "nvlink_bytes_per_gpu": Bn,
                "halo_GBps_per_gpu": round(B / us / 1e3, 1) if us else None, "roofline_us": round(t_roof, 2),
                "roofline_frac": round(t_roof / us, 3) if us else None,

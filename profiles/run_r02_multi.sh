@@ -11,7 +11,7 @@ if [ "$PARITY" = "full" ]; then
   for m in auto ll128 fence; do
     extra=""; [ "$m" = "auto" ] && extra="IGG_BULK_THRESHOLD=16384"
     t0=$(date +%s)
-    env IGG_MODE=$m $extra timeout 500 $TR --nproc-per-node $N --master-port 2954$N tests/mp_worker.py > gpurun_out/mp${N}_${m}_r02.log 2>&1
+    env IGG_MODE=$m IGG_DIRECT_THRESHOLD=0 $extra timeout 500 $TR --nproc-per-node $N --master-port 2954$N tests/mp_worker.py > gpurun_out/mp${N}_${m}_r02.log 2>&1
     echo "mp$N $m rc=$? $(( $(date +%s) - t0 ))s: $(grep -c MISMATCH gpurun_out/mp${N}_${m}_r02.log) mismatch lines; $(grep MP_WORKER_OK gpurun_out/mp${N}_${m}_r02.log)"
     grep -v "^\*\|OMP_NUM\|^W1\|^$" gpurun_out/mp${N}_${m}_r02.log | tail -4
   done

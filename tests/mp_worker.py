@@ -44,6 +44,9 @@ def case_list(n):
         # staging growth: a much bigger field after the small ones, then small again
         ((96, 80, 72), dict(periodx=1, periody=1, periodz=1), [(96, 80, 72), (97, 80, 72)], None, 8, (3, 1, 2), 3),
         ((nx, ny, nz), dict(periodx=1, periody=1, periodz=1), [(nx, ny, nz)], None, 1, (2, 1), 2),
+        # rows of 1 KiB and more: with fields from igg.alloc_field the y/z faces go straight into the neighbour's halo
+        ((160, 12, 10), dict(periodx=1, periody=1, periodz=1), [(160, 12, 10), (161, 12, 10)], None, 8, (3, 1, 2), 3),
+        ((260, 12, 10), dict(periody=1, overlaps=(2, 4, 2), halowidths=(1, 2, 1)), [(260, 12, 10), (260, 13, 10), (260, 12, 11)], None, 4, (3, 1, 2), 2),
     ]
     return cases
 
@@ -155,6 +158,22 @@ def main():
                 if not torch.equal(a, b):
                     ok = False
                     print(f"GRAPH/STREAM MISMATCH case {ci} rank {me} field {i}", flush=True)
+        # The same calls on fields inside symmetric allocations (igg.alloc_field): boxes that span x with rows of
+        # 1 KiB or more are stored straight into the neighbour's field (direct-to-halo), the rest is staged as before.
+        # Same bits as the staged result, which is checked against the oracle below.
+        td = [igg.alloc_field(s_, dtype=TDT[elsize]) for s_ in shapes]
+        for rep in list(range(reps)) + [-1]:
+            load(td, rep)
+            igg.update_halo(*[(t, hw) for t, hw in zip(td, hws_)], dims=dims, blocking=(rep % 2 == 0))
+        torch.cuda.synchronize()
+        for i, (a, b) in enumerate(zip(td, ts)):
+            if not torch.equal(a, b):
+                ok = False
+                print(f"DIRECT/STAGED MISMATCH case {ci} rank {me} field {i}: {int((a != b).sum())} cells", flush=True)
+        dist.barrier()
+        for t in td:
+            igg.free_field(t)
+        del td
         if tn is not None:
             for i, (a, b) in enumerate(zip(tn, ts)):
                 if not torch.equal(a, b):
@@ -236,7 +255,11 @@ def main():
     a = igg.zeros((N, N, N), dtype=torch.int64)
     a.copy_(torch.randint(-2**62, 2**62, (N, N, N), dtype=torch.int64, device="cuda", generator=gen))
     b = a.clone(memory_format=torch.preserve_format)
+    c = igg.alloc_field((N, N, N), dtype=torch.int64)       # symmetric allocation: y/z faces direct-to-halo
+    c.copy_(a)
     igg.update_halo(a)
+    igg.update_halo(c, blocking=False)
+    igg.update_halo(c)
     igg.set_exchange_mode("nccl")
     igg.update_halo(b)
     igg.set_exchange_mode(IPC_MODE)
@@ -244,6 +267,12 @@ def main():
     if not torch.equal(a, b):
         ok = False
         print(f"FULL-SIZE fused/NCCL MISMATCH rank {me}", flush=True)
+    if not torch.equal(a, c):
+        ok = False
+        print(f"FULL-SIZE direct/staged MISMATCH rank {me}: {int((a != c).sum())} cells", flush=True)
+    dist.barrier()
+    igg.free_field(c)
+    del c
     for d in range(3):
         right = g.neighbors[1][d]
         left = g.neighbors[0][d]
@@ -273,8 +302,22 @@ def main():
     for t in fa:
         t.copy_(torch.randint(-2**62, 2**62, tuple(t.shape), dtype=torch.int64, device="cuda", generator=gen))
     fb = [t.clone(memory_format=torch.preserve_format) for t in fa]
+    fc = [igg.alloc_field(s_, dtype=torch.int64) for s_ in shapes4]     # symmetric allocations: z-faces direct-to-halo
+    for x, y in zip(fc, fa):
+        x.copy_(y)
     igg.update_halo(*fa, blocking=False)
     igg.update_halo(*fa)                          # twice: both staging halves, halos must not change
+    for rep in range(3):
+        igg.update_halo(*fc, blocking=(rep == 2))
+    torch.cuda.synchronize()
+    for i, (x, y) in enumerate(zip(fc, fa)):
+        if not torch.equal(x, y):
+            ok = False
+            print(f"FULL-SIZE z-row direct/staged MISMATCH rank {me} field {i}: {int((x != y).sum())} cells", flush=True)
+    dist.barrier()
+    for x in fc:
+        igg.free_field(x)
+    del fc
     igg.set_exchange_mode("nccl")
     igg.update_halo(*fb)
     igg.set_exchange_mode(IPC_MODE)

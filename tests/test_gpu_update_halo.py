@@ -524,3 +524,30 @@ def test_big_self_wraps_bulk_copy_pipeline(mode, monkeypatch):
         tiles, _ = L.plan_tiles(gg.desc, [L.make_field(t.data_ptr(), tuple(t.shape), gg.halowidths, 8) for t in ts], (3, 1, 2), L.IGG_MODE_IPC_1PHASE)
         assert any(t.bulk for t in tiles) and any(not t.bulk for t in tiles)
     igg.finalize_global_grid()
+
+
+def test_symmetric_field_allocation_single_rank():
+    """igg_alloc_field / igg_free_field through the host mirror: zero-initialised column-major arrays that update_halo!
+    treats like any other device array (with one rank there is no neighbour to store into), slots are reused."""
+    kw = dict(periodx=1, periody=1, periodz=1)
+    igg.init_global_grid(160, 12, 10, quiet=True, **kw)
+    (g,) = O.make_grids(1, 160, 12, 10, **kw)
+    a = O.random_bits_field((160, 12, 10), 8, 77)
+    want = a.copy(order="F")
+    O.update_halo([g], [[want]])
+    t = igg.alloc_field((160, 12, 10), dtype=torch.int64)
+    assert int(t.abs().sum()) == 0 and tuple(t.shape) == (160, 12, 10) and t.stride() == (1, 160, 1920)
+    t.copy_(igg.from_numpy(a))
+    u = igg.alloc_field((161, 12, 10), dtype=torch.int64)
+    igg.update_halo(t)
+    assert bits_equal(t, want)
+    p_t = t.data_ptr()
+    igg.free_field(t)
+    v = igg.alloc_field((160, 12, 10), dtype=torch.int64)       # the freed slot is handed out again
+    v.copy_(igg.from_numpy(a))
+    igg.update_halo(v, u)
+    assert bits_equal(v, want)
+    with pytest.raises(KeyError):
+        igg.free_field(torch.zeros(4, device="cuda"))
+    del p_t
+    igg.finalize_global_grid()                                  # releases u and v

@@ -13,7 +13,7 @@ from igg_b200 import _lib as L
 from oracle import igg_oracle as O
 from test_plan_vs_oracle import desc_of, flat_bytes, rand_field
 
-PUSH, LOCAL, UNPACK, PUSH_LL, UNPACK_LL, WRAPX = 0, 1, 2, 6, 7, 8
+PUSH, LOCAL, UNPACK, PUSH_LL, UNPACK_LL, WRAPX, PUSH_DIRECT, WAIT = 0, 1, 2, 6, 7, 8, 9, 10
 LINE, PAYLOAD = 128, 120
 OFFSETS = [(ox, oy, oz) for oz in (-1, 0, 1) for oy in (-1, 0, 1) for ox in (-1, 0, 1)]   # index = (ox+1)+3(oy+1)+9(oz+1)
 
@@ -64,21 +64,21 @@ def box_offset(t, pb):
     return t.src_off + y * t.src_sy + z * t.src_sz + c
 
 
-def run_tables(grids, fields_per_rank, hws, dims, mode, epoch=7):
+def run_tables(grids, fields_per_rank, hws, dims, mode, epoch=7, direct=False):
     n = len(grids)
     mem = [[flat_bytes(A) for A in fr] for fr in fields_per_rank]
     tables, stagings = [], []
     for r, g in enumerate(grids):
         cf = [L.make_field(0x10000 * (i + 1), A.shape, hws[i], A.dtype.itemsize) for i, A in enumerate(fields_per_rank[r])]
-        tiles, stg = L.plan_tiles(desc_of(g), cf, dims, mode)
+        tiles, stg = L.plan_tiles(desc_of(g), cf, dims, mode | (0x100 if direct else 0))
         tables.append(tiles)
         stagings.append(np.full(max(stg, 1), 0xEE, dtype=np.uint8))
     kinds = {t.kind for tb in tables for t in tb}
-    assert kinds <= ({PUSH_LL, LOCAL, WRAPX, UNPACK_LL} if mode == L.IGG_MODE_IPC_LL128 else {PUSH, LOCAL, WRAPX, UNPACK})
+    assert kinds <= ({PUSH_LL, LOCAL, WRAPX, UNPACK_LL} if mode == L.IGG_MODE_IPC_LL128 else {PUSH, LOCAL, WRAPX, UNPACK}) | ({PUSH_DIRECT, WAIT} if direct else set())
     ep = np.frombuffer(np.uint64(epoch).tobytes(), dtype=np.uint8)
     for r, g in enumerate(grids):                       # everything that does not wait
         order = [t.kind for t in tables[r]]
-        assert order == sorted(order, key=lambda k: {PUSH: 0, PUSH_LL: 0, WRAPX: 1, LOCAL: 1, UNPACK: 2, UNPACK_LL: 2}[k])
+        assert order == sorted(order, key=lambda k: {PUSH: 0, PUSH_LL: 0, PUSH_DIRECT: 0, WRAPX: 1, LOCAL: 1, UNPACK: 2, UNPACK_LL: 2, WAIT: 2}[k])
         for t in tables[r]:
             if t.kind == PUSH:
                 copy_rows(t, mem[r][t.field], stagings[peer_of(g, t.nbr)])
@@ -86,6 +86,11 @@ def run_tables(grids, fields_per_rank, hws, dims, mode, epoch=7):
                 copy_rows(t, mem[r][t.field], mem[r][t.field])
             elif t.kind == WRAPX:
                 wrap_x(t, mem[r][t.field])
+            elif t.kind == PUSH_DIRECT:     # straight into the neighbour's copy of the field; it must expect that tile
+                q = peer_of(g, t.nbr)
+                copy_rows(t, mem[r][t.field], mem[q][t.field])
+                waits = [w for w in tables[q] if w.kind == WAIT and w.nbr == 26 - t.nbr and w.flag_idx == t.flag_idx]
+                assert len(waits) == 1 and waits[0].field == t.field
             elif t.kind == PUSH_LL:
                 W, nbytes, stg = 1 << t.vec_log2, t.dst_sy, stagings[peer_of(g, t.nbr)]
                 assert t.ncols % W == 0 and nbytes % W == 0 and t.dst_off % LINE == 0
@@ -218,7 +223,7 @@ def test_every_tile_stays_inside_its_offsets_region(case, mode):
         for o in range(27):
             assert reg["byte_pack"][o] == sum(reg["byte_need"][:o]) and reg["flag_pack"][o] == sum(reg["flag_need"][:o])
         for t in tiles:
-            if t.kind in (LOCAL, WRAPX):
+            if t.kind in (LOCAL, WRAPX, PUSH_DIRECT, WAIT):
                 continue
             o = 26 - t.nbr if t.kind in (PUSH, PUSH_LL) else t.nbr
             lo, hi = staged_range(t)
@@ -239,3 +244,36 @@ def test_tile_tables_match_golden(ci, case, mode):
     for r in range(case["nprocs"]):
         for a, w in zip(fields[r], G.arrays(ci, r, "out")):
             assert np.array_equal(a, w), (case["name"], r)
+
+
+DIRECT_CASES = [
+    (2, (160, 9, 10), dict(periodx=1, periody=1, periodz=1), [(160, 9, 10), (161, 9, 10)], None, 8, (3, 1, 2)),
+    (4, (160, 9, 10), dict(), [(160, 9, 10), (160, 10, 10), (160, 9, 11)], None, 8, (3, 1, 2)),
+    (8, (130, 9, 10), dict(periodx=1, periodz=1, overlaps=(4, 2, 3), halowidths=(2, 1, 1)), [(130, 9, 10), (131, 9, 10)], None, 8, (3, 1, 2)),
+    (8, (300, 12, 10), dict(periodx=1, periody=1, periodz=1), [(300, 12, 10)], None, 4, (3, 1, 2)),
+    (4, (2100, 40, 1), dict(periodx=1, periody=1, dimx=1, dimy=4), [(2100, 40)], None, 8, (3, 1, 2)),     # rows longer than a tile
+    (2, (160, 9, 10), dict(dimx=1, dimy=1, dimz=2, periodx=1, periody=1, periodz=1), [(160, 9, 10)], None, 8, (3,)),
+    (8, (13, 9, 10), dict(periodx=1, periody=1, periodz=1), [(13, 9, 10)], None, 8, (3, 1, 2)),           # too narrow: all staged
+]
+
+
+@pytest.mark.parametrize("mode", [L.IGG_MODE_IPC_1PHASE, L.IGG_MODE_IPC_LL128], ids=["fence", "ll128"])
+@pytest.mark.parametrize("case", DIRECT_CASES, ids=[f"d{i}" for i in range(len(DIRECT_CASES))])
+def test_direct_to_halo_tile_tables_match_oracle(case, mode):
+    """Fields in symmetric allocations: boxes that span x (rows of at least 1 KiB) are stored straight into the
+    neighbour's field (PUSH_DIRECT, paired with exactly one WAIT tile there), everything else stays staged."""
+    nprocs, gsz, kw, shapes, hws, elsize, dims = case
+    grids = O.make_grids(nprocs, *gsz, **kw)
+    hws = hws or [grids[0].halowidths] * len(shapes)
+    base = [[rand_field(s, elsize, 2000 * r + 10 * i + 5) for i, s in enumerate(shapes)] for r in range(nprocs)]
+    want = [[a.copy(order="F") for a in fr] for fr in base]
+    O.update_halo(grids, [[(a, hws[i]) for i, a in enumerate(fr)] for fr in want], dims=dims)
+    got = [[a.copy(order="F") for a in fr] for fr in base]
+    run_tables(grids, got, hws, dims, mode, direct=True)
+    for r in range(nprocs):
+        for i in range(len(shapes)):
+            assert np.array_equal(flat_bytes(got[r][i]), flat_bytes(want[r][i])), (r, i)
+    cf = [L.make_field(0x10000 * (i + 1), s, hws[i], elsize) for i, s in enumerate(shapes)]
+    tiles, _ = L.plan_tiles(desc_of(grids[0]), cf, dims, mode | 0x100)
+    wide = shapes[0][0] * elsize >= 1024 and (grids[0].dims[1] > 1 or grids[0].dims[2] > 1)     # a y or z neighbour is another rank
+    assert any(t.kind == PUSH_DIRECT for t in tiles) == wide
