@@ -5,6 +5,7 @@
 // (arrival flags + counters), the double-buffered receive staging, cached plans and peer mappings; user arrays are
 // only borrowed for the duration of a call.
 #include <cuda_runtime.h>
+#include <dlfcn.h>
 #include <time.h>
 #include <unistd.h>
 
@@ -52,6 +53,7 @@ struct PeerSeg {
     bool ipc = false;
     int64_t bytes = 0;
     uint64_t raw = 0;             // the owner's own address of the segment (identity check)
+    cudaIpcMemHandle_t handle = {};   // ... and its IPC handle (the same address may be handed out again for another allocation)
 };
 
 struct Peer {
@@ -59,6 +61,23 @@ struct Peer {
     int device = -1;
     PeerSeg ctrl, staging, gather;
 };
+
+// Base address and size of the device allocation `p` lies in (driver API, looked up at run time: the library links
+// the CUDA runtime only).  false if it cannot be told.
+static bool device_address_range(const void* p, void** base, size_t* bytes) {
+    typedef int (*fn_t)(unsigned long long*, size_t*, unsigned long long);
+    static fn_t fn = [] {
+        void* h = dlopen("libcuda.so.1", RTLD_NOW | RTLD_GLOBAL);
+        return h ? reinterpret_cast<fn_t>(dlsym(h, "cuMemGetAddressRange_v2")) : nullptr;
+    }();
+    if (!fn) return false;
+    unsigned long long b = 0;
+    size_t n = 0;
+    if (fn(&b, &n, (unsigned long long)(uintptr_t)p) != 0 || !b) return false;
+    *base = reinterpret_cast<void*>((uintptr_t)b);
+    *bytes = n;
+    return true;
+}
 
 static uint64_t process_nonce() {
     static uint64_t nonce = [] {
@@ -127,6 +146,7 @@ struct igg_ctx {
     char* gather_buf = nullptr;   int64_t gather_bytes = 0;       // root: device image of A_global (peer mapped)
     char* gather_src = nullptr;   int64_t gather_src_bytes = 0;   // staging for host-resident A
     TileRec* d_gather_tiles = nullptr; int gather_tiles_cap = 0;
+    int64_t gather_tile_key[8] = {0}; int gather_ntiles = 0;     // what the table on the device was built for
     // NCCL comparison path (nccl_path.cu)
     NcclPath* nccl = nullptr;
     // optional kernel timeline (igg_trace_enable)
@@ -1155,17 +1175,56 @@ int igg_gather(igg_ctx* ctx, const void* A, const int64_t sizeA_in[3], int ndims
         return IGG_OK;
     }
 
-    // Round 1 of the hand-shake: root's verdict and whether its device image of A_global must grow.
-    const bool regrow_mine = is_root && !status && bytesG > ctx->gather_bytes;
-    std::vector<SegPayload> all;
+    // Round 1 of the hand-shake: root's verdict and where the blocks go.  If root's A_global is device memory whose
+    // allocation can be exported over CUDA IPC (cudaMalloc'ed: torch's caching allocator, igg_alloc_field, CUDA.jl with
+    // the non-pool allocator), every rank stores its block straight into A_global (as the reference's Gatherv places
+    // the blocks, ref: src/gather.jl:36-49).  Otherwise (host memory, stream-ordered pool memory) the blocks go into
+    // a device image owned by the context and root copies it out afterwards.
+    SegPayload mine;
+    std::memset(&mine, 0, sizeof(mine));
+    mine.proc_nonce = process_nonce();
+    mine.device = ctx->device;
+    mine.status = status;
+    snprintf(mine.msg, sizeof(mine.msg), "%s", msg);
+    bool direct = false;
+    long long direct_off = 0;
+    if (is_root && !status) {
+        static const bool gather_direct_on = !(getenv("IGG_GATHER_DIRECT") && getenv("IGG_GATHER_DIRECT")[0] == '0');
+        cudaPointerAttributes a;
+        void* base = nullptr;
+        size_t alloc_bytes = 0;
+        if (gather_direct_on && cudaPointerGetAttributes(&a, A_global) == cudaSuccess && a.type == cudaMemoryTypeDevice &&
+            a.device == ctx->device && device_address_range(A_global, &base, &alloc_bytes) &&
+            cudaIpcGetMemHandle(&mine.handle, base) == cudaSuccess) {
+            direct = true;
+            direct_off = static_cast<char*>(A_global) - static_cast<char*>(base);
+            mine.ptr = reinterpret_cast<uint64_t>(base);
+            mine.bytes = (int64_t)alloc_bytes;
+            snprintf(mine.msg, sizeof(mine.msg), "D%lld", direct_off);
+        } else {
+            cudaGetLastError();
+        }
+    }
+    const bool regrow_mine = is_root && !status && !direct && bytesG > ctx->gather_bytes;
+    if (is_root && !direct) {
+        if (ctx->gather_buf && !regrow_mine) {
+            CU(cudaIpcGetMemHandle(&mine.handle, ctx->gather_buf));
+            mine.ptr = reinterpret_cast<uint64_t>(ctx->gather_buf);
+        }
+        mine.bytes = regrow_mine ? -1 : ctx->gather_bytes;
+    }
+    std::vector<SegPayload> all(g.nprocs);
     int rc;
     {
-        const int64_t keep = ctx->gather_bytes;
-        rc = exchange_segment(ctx, 1, regrow_mine ? -1 : keep, status, msg, all);
+        std::vector<char> raw;
+        rc = ctx->cp.allgather(&mine, raw);
         if (rc) return rc;
+        std::memcpy(all.data(), raw.data(), raw.size());
     }
     if (all[root].status) return fail(all[root].status, "%s", all[root].msg[0] ? all[root].msg : "gather!: root reported an error.");
-    if (all[root].bytes < 0) {
+    direct = all[root].msg[0] == 'D';
+    if (direct) direct_off = atoll(all[root].msg + 1);
+    if (!direct && all[root].bytes < 0) {
         // Root replaces its buffer: peers drop the old mapping first, then root reallocates and publishes the new one.
         if (!is_root) close_segment(ctx->peers[root].gather);
         rc = ctx->cp.barrier();
@@ -1182,17 +1241,19 @@ int igg_gather(igg_ctx* ctx, const void* A, const int64_t sizeA_in[3], int ndims
     const SegPayload& rp = all[root];
     char* dst_base = nullptr;
     if (is_root) {
-        dst_base = ctx->gather_buf;
+        dst_base = direct ? static_cast<char*>(A_global) : ctx->gather_buf;
     } else {
         Peer& pr = ctx->peers[root];
-        if (pr.gather.ptr && pr.gather.raw != rp.ptr) close_segment(pr.gather);
+        if (pr.gather.ptr && (pr.gather.raw != rp.ptr || std::memcmp(&pr.gather.handle, &rp.handle, sizeof(rp.handle)) != 0))
+            close_segment(pr.gather);                                                 // another allocation than last time
         if (!pr.gather.ptr) {
             rc = open_segment(ctx, pr, rp.handle, rp.ptr, pr.gather);
             if (rc) return rc;
             pr.gather.bytes = rp.bytes;
             pr.gather.raw = rp.ptr;
+            pr.gather.handle = rp.handle;
         }
-        dst_base = pr.gather.ptr;
+        dst_base = pr.gather.ptr + (direct ? direct_off : 0);
     }
 
     // Source block: device memory as is, host memory through a device staging copy.
@@ -1218,19 +1279,29 @@ int igg_gather(igg_ctx* ctx, const void* A, const int64_t sizeA_in[3], int ndims
     // Global sizes are known to every rank from dims and sizeA (ref: src/gather.jl:33).
     int64_t gsz[2] = {sizeA[0] * g.dims[0], sizeA[1] * g.dims[1]};
     int64_t origin[3] = {g.coords[0] * sizeA[0], g.coords[1] * sizeA[1], g.coords[2] * sizeA[2]};
-    std::vector<TileRec> tiles;
-    build_block_copy_tiles(elsize, sizeA, gsz, origin, (int64_t)((uintptr_t)src % 16), 0, tiles);
-    if ((int)tiles.size() > ctx->gather_tiles_cap) {
-        CU(cudaDeviceSynchronize());
-        if (ctx->d_gather_tiles) CU(cudaFree(ctx->d_gather_tiles));
-        CU(cudaMalloc(&ctx->d_gather_tiles, tiles.size() * sizeof(TileRec)));
-        ctx->gather_tiles_cap = (int)tiles.size();
+    // The tile table only depends on the block shape, the element size, my place in the global array and the source
+    // alignment: kept on the device from call to call.
+    const int64_t tkey[8] = {sizeA[0], sizeA[1], sizeA[2], elsize, origin[0] + (origin[1] << 20) + (origin[2] << 40), gsz[0], gsz[1],
+                             (int64_t)((uintptr_t)src % 16)};
+    if (std::memcmp(tkey, ctx->gather_tile_key, sizeof(tkey)) != 0 || ctx->gather_ntiles == 0) {
+        std::vector<TileRec> tiles;
+        build_block_copy_tiles(elsize, sizeA, gsz, origin, (int64_t)((uintptr_t)src % 16), 0, tiles);
+        CU(cudaDeviceSynchronize());             // an earlier gather's kernel may still read the old table
+        if ((int)tiles.size() > ctx->gather_tiles_cap) {
+            if (ctx->d_gather_tiles) CU(cudaFree(ctx->d_gather_tiles));
+            CU(cudaMalloc(&ctx->d_gather_tiles, tiles.size() * sizeof(TileRec)));
+            ctx->gather_tiles_cap = (int)tiles.size();
+        }
+        const cudaError_t e = upload_now(ctx->d_gather_tiles, tiles.data(), tiles.size() * sizeof(TileRec));
+        if (e != cudaSuccess) return fail(IGG_ERR_CUDA, "gather!: tile table upload failed: %s", cudaGetErrorString(e));
+        std::memcpy(ctx->gather_tile_key, tkey, sizeof(tkey));
+        ctx->gather_ntiles = (int)tiles.size();
     }
-    CU(cudaMemcpyAsync(ctx->d_gather_tiles, tiles.data(), tiles.size() * sizeof(TileRec), cudaMemcpyHostToDevice, stream));
+    const int ntiles = ctx->gather_ntiles;
     KParams p;
     std::memset(&p, 0, sizeof(p));
     p.tiles = ctx->d_gather_tiles;
-    p.n_tiles = (int32_t)tiles.size();
+    p.n_tiles = (int32_t)ntiles;
     p.n_push_tiles = 0;
     p.field[0] = const_cast<char*>(src);
     p.copy_dst[0] = dst_base;
@@ -1238,12 +1309,12 @@ int igg_gather(igg_ctx* ctx, const void* A, const int64_t sizeA_in[3], int ndims
     p.status = ctx->d_status;
     p.timeout_ns = ctx->timeout_ns;
     order_after_previous(ctx, stream);
-    rc = launch_halo_kernel(p, (int)std::min<int64_t>((int64_t)tiles.size(), (int64_t)ctx->max_blocks * 4), stream);
+    rc = launch_halo_kernel(p, (int)std::min<int64_t>((int64_t)ntiles, (int64_t)ctx->max_blocks * 4), stream);
     if (rc) return rc;
     remember_launch(ctx, stream);
     CU(cudaStreamSynchronize(stream));       // my block has landed in root's memory
     rc = ctx->cp.barrier();                  // ... and so has everyone else's
-    if (rc) return rc;
+    if (rc || direct) return rc;             // straight into A_global: done (the next gather starts with a barrier)
     if (is_root) {
         CU(cudaMemcpyAsync(A_global, ctx->gather_buf, (size_t)bytesG, cudaMemcpyDefault, stream));
         CU(cudaStreamSynchronize(stream));

@@ -150,6 +150,7 @@ struct Plan {
     int64_t  remote_bytes = 0;                       // payload bytes of all staging slots (the same on every rank)
     bool     global_active = false;                  // some rank exchanges with another rank in this call (rank-independent)
     bool     has_bulk = false;                       // some tile is flagged for the bulk-copy pipeline
+    bool     small_tiles = false;                    // input: keep every tile at kTileBytes (igg_update_halo_noalloc's limit counts those)
     int64_t  local_bytes = 0;                        // bytes of all self-wrap boxes of this rank
     int32_t  n_push_tiles = 0;
     uint32_t n_flags = 0;                           // arrival flags this plan uses (must be <= kMaxFlags)

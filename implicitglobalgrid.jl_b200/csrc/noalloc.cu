@@ -18,7 +18,12 @@
 //    the start of every call and the table is rewritten, in stream order.  Two calls whose work overlaps on the GPU
 //    (different streams, or different host threads) would overwrite each other's table: do not do that.
 //  * the first call on a device looks up the array's device address (once per device); make that first call
-//    before starting any stream capture.
+//    before starting any stream capture;
+//  * a call on a stream that is being captured is refused (IGG_ERR_UNSUPPORTED): the table is copied from host
+//    memory that only lives for the duration of the call;
+//  * the call makes desc->device the current device and leaves it so; a call whose plan differs from the previous
+//    call's on that device copies the new table from ordinary host memory, which makes even an IGG_ASYNC call wait
+//    for earlier work on the stream -- repeated calls with the same shapes skip the copy and are truly stream-ordered.
 #include <cuda_runtime.h>
 
 #include <mutex>
@@ -39,6 +44,14 @@ static __device__ __align__(256) unsigned char g_noalloc_scratch[kScratchBytes];
 std::mutex g_mutex;
 unsigned char* g_scratch_ptr[kMaxDevices] = {nullptr};   // per device, filled at set-up
 int g_max_blocks[kMaxDevices] = {0};
+// What the table in the array was built from, per device: a call with the same key finds its table already there.
+struct TableKey {
+    igg_grid_desc desc;
+    int nfields, mask;
+    igg::FieldKey field[IGG_MAX_FIELDS];
+    bool valid;
+};
+TableKey g_last[kMaxDevices];
 
 // Once per device, with that device current.
 int setup_device(int device, unsigned char** ptr_out, int* max_blocks_out) {
@@ -79,6 +92,13 @@ extern "C" int igg_update_halo_noalloc(const igg_grid_desc* desc, int nfields, c
     int mask;
     int rc = dims_mask_from_order(dims_order, ndims_order, &mask);
     if (rc) return rc;
+    {
+        cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+        if (cudaStreamIsCapturing(static_cast<cudaStream_t>(stream_v), &cs) != cudaSuccess) cudaGetLastError();
+        else if (cs != cudaStreamCaptureStatusNone)
+            return fail(IGG_ERR_UNSUPPORTED, "igg_update_halo_noalloc: the stream is being captured; this entry point cannot "
+                                             "be recorded into a CUDA graph (use igg_update_halo / igg_update_halo_prepared).");
+    }
     e = cudaSetDevice(desc->device);
     if (e != cudaSuccess) return fail(IGG_ERR_CUDA, "cudaSetDevice(%d) failed: %s", desc->device, cudaGetErrorString(e));
 
@@ -98,6 +118,7 @@ extern "C" int igg_update_halo_noalloc(const igg_grid_desc* desc, int nfields, c
     }
 
     Plan plan;                                  // host-side only
+    plan.small_tiles = true;                    // the limit below counts tiles of 8 KiB
     rc = build_plan(*desc, nfields, f, mask, plan);
     if (rc) return rc;
     if (plan.tiles.empty()) return IGG_OK;
@@ -112,12 +133,33 @@ extern "C" int igg_update_halo_noalloc(const igg_grid_desc* desc, int nfields, c
     if (rc) return rc;
 
     cudaStream_t stream = static_cast<cudaStream_t>(stream_v);
-    // The array keeps whatever the last call left: clear the control words, then write this call's table.
-    e = cudaMemsetAsync(scratch, 0, kControlBytes, stream);
-    if (e != cudaSuccess) return fail(IGG_ERR_CUDA, "igg_update_halo_noalloc: clearing the scratch failed: %s", cudaGetErrorString(e));
-    e = cudaMemcpyAsync(scratch + kControlBytes, plan.tiles.data(), plan.tiles.size() * sizeof(TileRec),
-                        cudaMemcpyHostToDevice, stream);
-    if (e != cudaSuccess) return fail(IGG_ERR_CUDA, "igg_update_halo_noalloc: writing the tile table failed: %s", cudaGetErrorString(e));
+    // The array keeps whatever the last call left.  If that is this very table (same grid, shapes, halowidths, element
+    // size, alignment and dims as the previous call on this device), it is used as it is; else the control words are
+    // cleared and the new table is written, in stream order (earlier calls' kernels are done with the old one by then).
+    TableKey key;
+    std::memset(&key, 0, sizeof(key));
+    key.desc = *desc;
+    key.nfields = nfields;
+    key.mask = mask;
+    for (int i = 0; i < nfields; ++i) key.field[i] = plan.key[i];
+    key.valid = true;
+    bool same;
+    {
+        std::lock_guard<std::mutex> lock(g_mutex);
+        same = g_last[desc->device].valid && std::memcmp(&g_last[desc->device], &key, sizeof(key)) == 0;
+        g_last[desc->device].valid = false;     // until the new table is known to be on its way
+    }
+    if (!same) {
+        e = cudaMemsetAsync(scratch, 0, kControlBytes, stream);
+        if (e != cudaSuccess) return fail(IGG_ERR_CUDA, "igg_update_halo_noalloc: clearing the scratch failed: %s", cudaGetErrorString(e));
+        e = cudaMemcpyAsync(scratch + kControlBytes, plan.tiles.data(), plan.tiles.size() * sizeof(TileRec),
+                            cudaMemcpyHostToDevice, stream);
+        if (e != cudaSuccess) return fail(IGG_ERR_CUDA, "igg_update_halo_noalloc: writing the tile table failed: %s", cudaGetErrorString(e));
+    }
+    {
+        std::lock_guard<std::mutex> lock(g_mutex);
+        g_last[desc->device] = key;
+    }
 
     KParams p;
     std::memset(&p, 0, sizeof(p));
@@ -125,6 +167,8 @@ extern "C" int igg_update_halo_noalloc(const igg_grid_desc* desc, int nfields, c
     p.n_tiles = (int32_t)plan.tiles.size();
     p.n_push_tiles = 0;                                   // one rank: LOCAL tiles only
     for (int i = 0; i < nfields; ++i) p.field[i] = f[i].ptr;
+    // One rank: the plan has only LOCAL / WRAPX tiles, nothing ever waits, so the flag array and the status word
+    // below are never touched by the kernel; they point into the scratch so that they are valid device addresses.
     p.local_flags = reinterpret_cast<const unsigned long long*>(scratch);
     p.status = reinterpret_cast<int*>(scratch + 3968);
     p.timeout_ns = 1000000000ull;

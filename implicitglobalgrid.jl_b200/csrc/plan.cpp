@@ -360,7 +360,7 @@ int build_plan(const igg_grid_desc& g, int nfields, const igg_field* fields, int
     plan.tile_bytes = (int32_t)tb;
     // Self-wraps: 8-KiB tiles (the latency regime's tuning) until a call wraps more than 8 MiB, then growing alike.
     int64_t tbl = kTileBytes;
-    if (plan.local_bytes > ((int64_t)8 << 20))
+    if (plan.local_bytes > ((int64_t)8 << 20) && !plan.small_tiles)
         while (tbl < kMaxBulkTileBytes && plan.local_bytes / tbl > 512) tbl *= 2;
     // Arrival flags: one per tile.  A slot reserves an upper bound of the tiles any box that fits it can have
     // (every full tile covers more than kTileBytes/2 bytes), so that flag numbers too are identical on every rank.

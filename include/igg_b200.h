@@ -167,7 +167,11 @@ int igg_free_field(igg_ctx* ctx, void* ptr);
  * IGG_ERR_ARG with a message naming the limit.  All calls share the one array, which keeps the last call's contents:
  * every call clears its control words and rewrites the table in stream order, so calls whose GPU work overlaps
  * (different streams or host threads) race -- serialise them.  The first call on a device resolves the array's
- * device address once; issue that first call before any stream capture begins.  `flags` as for igg_update_halo. */
+ * device address once; issue that first call before any stream capture begins.  A call on a stream that is being
+ * captured is refused with IGG_ERR_UNSUPPORTED (the table is copied from host memory that only lives during the
+ * call).  The call makes desc->device current and leaves it current.  With IGG_ASYNC a call whose plan differs from the
+ * previous one on that device still waits for earlier work on the stream (the new table comes from ordinary host
+ * memory); repeating the same shapes reuses the table and is stream-ordered.  `flags` as for igg_update_halo. */
 #define IGG_NOALLOC_MAX_TILES 3200
 int     igg_update_halo_noalloc(const igg_grid_desc* desc, int nfields, const igg_field* fields,
                                 const int* dims_order, int ndims_order, void* stream, int flags);

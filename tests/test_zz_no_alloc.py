@@ -103,3 +103,31 @@ def test_refuses_what_does_not_fit_and_multi_rank_grids():
     d2.nprocs = 2
     rc = _call_noalloc(d2, fields[:1], [g.halowidths])
     assert rc == L.IGG_ERR_UNSUPPORTED and "nprocs == 1" in lib.igg_last_error().decode()
+
+
+def test_allocates_nothing_and_refuses_stream_capture():
+    """The point of the entry point: device memory in use does not change across calls (first call of a plan, repeated
+    call, a different plan), and a call on a capturing stream is refused instead of recording a copy from host memory
+    that is gone when the graph is replayed."""
+    igg.init_global_grid(40, 24, 18, periodx=1, periody=1, periodz=1, quiet=True)
+    g = igg.global_grid()
+    a = [_random_field((40, 24, 18), 7), _random_field((41, 24, 18), 8)]
+    hws = [g.halowidths] * 2
+    L.check(_call_noalloc(g.desc, a, hws))            # the first call on this device in this process may set up the runtime
+    torch.cuda.synchronize()
+    free0 = torch.cuda.mem_get_info()[0]
+    for _ in range(3):
+        L.check(_call_noalloc(g.desc, a, hws))
+    L.check(_call_noalloc(g.desc, a[:1], hws[:1], dims=(2, 3)))
+    L.check(_call_noalloc(g.desc, a, hws, flags=L.IGG_ASYNC))
+    torch.cuda.synchronize()
+    assert torch.cuda.mem_get_info()[0] == free0
+    s = torch.cuda.Stream()
+    graph = torch.cuda.CUDAGraph()
+    lib = L.load()
+    with torch.cuda.stream(s):
+        cf = [L.make_field(t.data_ptr(), tuple(t.shape), hw, 8) for t, hw in zip(a, hws)]
+        arr = (L.Field * 2)(*cf)
+        with torch.cuda.graph(graph, stream=s):
+            rc = lib.igg_update_halo_noalloc(C.byref(g.desc), 2, arr, None, 0, C.c_void_p(s.cuda_stream), L.IGG_ASYNC)
+    assert rc == L.IGG_ERR_UNSUPPORTED and "captured" in lib.igg_last_error().decode()
