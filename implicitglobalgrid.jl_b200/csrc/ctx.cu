@@ -1116,6 +1116,34 @@ int igg_debug_timed_calls(igg_prepared** calls, int ncalls, void* stream_v, int 
     return rc;
 }
 
+int igg_debug_peer_copy(igg_ctx* ctx, void* sym_ptr, int peer, size_t bytes, int reps, double* gbs_out) {
+    if (!ctx || !sym_ptr || !gbs_out || reps < 1) return fail(IGG_ERR_ARG, "igg_debug_peer_copy: invalid argument.");
+    long long off = 0;
+    const int slot = find_reg(ctx, sym_ptr, &off);
+    if (slot < 0 || peer < 0 || peer >= ctx->g.nprocs || peer == ctx->g.me || off + (long long)bytes > ctx->regs[slot].bytes)
+        return fail(IGG_ERR_ARG, "igg_debug_peer_copy: not a symmetric allocation of this context, or a bad peer / size.");
+    int rc = make_current(ctx);
+    if (rc) return rc;
+    char* dst = ctx->regs[slot].peer[peer].ptr + off;
+    cudaEvent_t e0, e1;
+    CU(cudaEventCreate(&e0));
+    CU(cudaEventCreate(&e1));
+    float best = 1e30f;
+    for (int r = 0; r <= reps; ++r) {               // the first one warms up
+        CU(cudaEventRecord(e0, 0));
+        CU(cudaMemcpyAsync(dst, sym_ptr, bytes, cudaMemcpyDeviceToDevice, 0));
+        CU(cudaEventRecord(e1, 0));
+        CU(cudaEventSynchronize(e1));
+        float ms = 0;
+        CU(cudaEventElapsedTime(&ms, e0, e1));
+        if (r > 0 && ms < best) best = ms;
+    }
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    *gbs_out = (double)bytes / (best * 1e-3) / 1e9;
+    return IGG_OK;
+}
+
 int igg_release_prepared(igg_prepared* h) {
     if (!h) return IGG_OK;
     if (h->ctx) {

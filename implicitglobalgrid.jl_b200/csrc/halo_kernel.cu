@@ -385,6 +385,7 @@ __device__ __forceinline__ void push_ll_tile(const TileRec& t, const char* __res
     typedef typename WordOf<W>::T Wt;
     const uint32_t j = threadIdx.x & 7u, g0 = threadIdx.x >> 3;
     const uint32_t nbytes = (uint32_t)t.dst_sy;
+    const bool narrow = t.ncols <= 16u;
     unsigned long long v[2][2];
 #pragma unroll
     for (int u = 0; u < 2; ++u) {
@@ -399,7 +400,9 @@ __device__ __forceinline__ void push_ll_tile(const TileRec& t, const char* __res
 #pragma unroll
                 for (int b = 0; b < 16; b += W) {
                     if (b < nb) {
-                        const unsigned long long w = *reinterpret_cast<const Wt*>(box + k.off);
+                        // strided x-face cells (the row is one word): ask L2 for 64 bytes, not the whole line
+                        const unsigned long long w = narrow ? (unsigned long long)ld_strided(reinterpret_cast<const Wt*>(box + k.off))
+                                                            : (unsigned long long)*reinterpret_cast<const Wt*>(box + k.off);
                         v[u][b >> 3] |= w << (8 * (b & 7));
                         box_step<W>(k, t.ncols, t.ny, t.src_sy, t.src_sz);
                     }

@@ -263,15 +263,17 @@ int64_t auto_bulk_threshold() {
     return v;
 }
 
-// Staged bytes per call from which fields in symmetric allocations are updated direct-to-halo.  Measured on 2 B200s
-// in a row along z (profiles/direct_ab_n2_r02.log): the ready hand-shake and the release fence make it slower than
-// LL128 staging for small calls (cfg2, 1 MiB: 16.0 vs 10.8 us), while from a few MiB on it wins by not unpacking
-// (cfg4 F = 1 / 2 / 4, 4 - 16 MiB: 33.7 / 61.2 / 115.6 vs 35.5 / 71.1 / 143.6 us).  IGG_DIRECT_THRESHOLD overrides it
-// (bytes; the same on every rank).
+// Staged bytes per call from which fields in symmetric allocations are updated direct-to-halo.  The ready hand-shake
+// and the release fence per tile make it slower than LL128 staging until the call is big enough for the saved unpack
+// pass to matter.  Measured: 2 B200s in a row along z (profiles/r02/direct_ab_n2_r02.log) cfg2, 1 MiB staged: 16.0 vs
+// 10.8 us; cfg4 F = 1 / 2 / 4 (4 / 8 / 16 MiB): 33.7 / 61.2 / 115.6 vs 35.5 / 71.1 / 143.6 us.  8 B200s, 2x2x2
+// (profiles/r02/configs_r02_n8_sym.jsonl vs profiles/configs_r02_n8.jsonl): cfg3ii periodic (12 MiB) 63.5 vs 39.8 us,
+// cfg4 F = 1 / 2 / 4 (12 / 24 / 48 MiB) 72.1 / 130.3 / 187.8 vs 43.5 / 97.9 / 209.4 us.  Hence 32 MiB.
+// IGG_DIRECT_THRESHOLD overrides it (bytes; the same on every rank).
 static int64_t direct_threshold() {
     static const int64_t v = [] {
         const char* e = getenv("IGG_DIRECT_THRESHOLD");
-        return (e && *e) ? (int64_t)atoll(e) : (int64_t)4 << 20;
+        return (e && *e) ? (int64_t)atoll(e) : (int64_t)32 << 20;
     }();
     return v;
 }

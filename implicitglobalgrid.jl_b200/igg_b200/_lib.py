@@ -101,6 +101,7 @@ def load():
         "igg_ctrl_selftest_run": (C.c_int, [vp, i32, i32, C.c_char_p, i32]),
         "igg_debug_state": (C.c_int, [vp, C.POINTER(C.c_uint64)]),
         "igg_debug_issue_loop": (C.c_int, [vp, vp, i32, C.POINTER(C.c_double)]),
+        "igg_debug_peer_copy": (C.c_int, [vp, vp, i32, C.c_size_t, i32, C.POINTER(C.c_double)]),
         "igg_debug_timed_calls": (C.c_int, [C.POINTER(vp), i32, vp, i32, i32, C.POINTER(C.c_float), C.POINTER(C.c_double)]),
         "igg_trace_enable": (C.c_int, [vp, i32]),
         "igg_trace_read": (C.c_int, [vp, C.POINTER(C.c_uint64), i32, i32p]),
@@ -119,7 +120,7 @@ DECLARED_SYMBOLS = [
     "igg_version", "igg_last_error", "igg_create", "igg_destroy", "igg_bootstrap_size", "igg_bootstrap_export",
     "igg_bootstrap_import", "igg_update_halo", "igg_prepare", "igg_update_halo_prepared", "igg_release_prepared", "igg_alloc_field", "igg_free_field", "igg_update_halo_noalloc", "igg_noalloc_scratch_bytes", "igg_set_mode", "igg_nccl_unique_id_size", "igg_nccl_get_unique_id",
     "igg_nccl_init", "igg_gather", "igg_diffusion3d_step", "igg_sendranges", "igg_recvranges", "igg_check_fields", "igg_plan_describe", "igg_plan_tiles",
-    "igg_ctrl_selftest_create", "igg_ctrl_selftest_run", "igg_debug_state", "igg_debug_issue_loop", "igg_debug_timed_calls", "igg_trace_enable", "igg_trace_read",
+    "igg_ctrl_selftest_create", "igg_ctrl_selftest_run", "igg_debug_state", "igg_debug_issue_loop", "igg_debug_peer_copy", "igg_debug_timed_calls", "igg_trace_enable", "igg_trace_read",
     "igg_launch_count", "igg_kernel_name",
 ]
 

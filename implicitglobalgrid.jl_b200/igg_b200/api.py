@@ -227,7 +227,8 @@ def alloc_field(shape, dtype=None):
     """A zero-initialised column-major array of Julia size `shape` inside a SYMMETRIC allocation (igg_alloc_field):
     collective -- every rank calls it with the same shape and dtype in the same order.  update_halo! then stores the
     y/z faces of such a field straight into the neighbours' halos over NVLink (direct-to-halo) instead of staging
-    and unpacking them.  Release it with free_field (collective) before finalize_global_grid, or let finalize do it."""
+    and unpacking them, for calls that stage 32 MiB or more per rank (IGG_DIRECT_THRESHOLD; smaller calls are faster
+    through LL128 staging).  Release it with free_field (collective) before finalize_global_grid, or let finalize do it."""
     torch = _torch()
     g = global_grid()
     shape = tuple(int(s) for s in (shape if isinstance(shape, (tuple, list)) else (shape,)))

@@ -150,7 +150,9 @@ int igg_release_prepared(igg_prepared* call);
  * for them: an allocation made here is SYMMETRIC (collective: every rank calls with the same size in the same order)
  * and mapped into every rank's address space through CUDA IPC, so that update_halo! of a field inside it stores every
  * send box that spans x (the y/z faces and the y-z edges: rows of at least 1 KiB) straight into the neighbour's halo
- * over NVLink; the strided x-faces and fields in foreign memory keep going through staging.  A field must lie at
+ * over NVLink -- for calls that stage at least 32 MiB per rank (IGG_DIRECT_THRESHOLD, bytes, the same on every rank;
+ * below that LL128 staging is the faster way, measured on 2 and 8 B200s) --; the strided x-faces and fields in foreign
+ * memory keep going through staging.  A field must lie at
  * the same offset of the same allocation on every rank (e.g. the k-th allocation holds array k everywhere).
  * Zero-initialised.  IGG_DIRECT=0 in the environment keeps everything staged (for comparison). */
 int igg_alloc_field(igg_ctx* ctx, size_t bytes, void** ptr_out);
@@ -281,6 +283,11 @@ int igg_debug_issue_loop(igg_prepared* call, void* stream, int n, double* ns_per
  * flags = IGG_SYNC: host clock around every host-synchronous call. */
 int igg_debug_timed_calls(igg_prepared** calls, int ncalls, void* stream, int steps, int flags, float* us_out,
                           double* loop_us_out);
+/* Peer-copy bandwidth over the mappings the exchange itself uses: copies `bytes` from this rank's copy of the symmetric
+ * allocation `sym_ptr` (igg_alloc_field) into rank `peer`'s copy with cudaMemcpyAsync, `reps` times, and returns the
+ * best GB/s (CUDA events).  The practical NVLink roof of this box for the roofline.  Not collective by itself, but
+ * every rank copying to its right neighbour at once is the exchange's traffic pattern. */
+int igg_debug_peer_copy(igg_ctx* ctx, void* sym_ptr, int peer, size_t bytes, int reps, double* gbs_out);
 /* Number of kernels this context has launched so far (the bench's `gpu_launches`). */
 int64_t igg_launch_count(const igg_ctx* ctx);
 /* Name of the kernel symbol the update path launches (for profiles). */

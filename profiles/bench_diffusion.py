@@ -39,19 +39,21 @@ def maxr(x):
 
 sim = Diffusion3D(n, n, n)
 out = {"config": f"diffusion3D {n}^3 f64 per GPU, non-periodic", "n_gpus": world, "dims": list(igg.global_grid().dims), "nt": nt}
-for fast, overlap in ((False, False), (False, True), (True, False), (True, True)):
+for fast, overlap, graph in ((False, False, False), (False, True, False), (True, False, False), (True, True, False),
+                             (False, False, True), (True, False, True), (True, True, True)):
     sim.fast = fast
-    sim.run(20, overlap=overlap)
+    sim._graphs.clear()                     # the captured kernels carry the arithmetic variant
+    sim.run(20, overlap=overlap, graph=graph)
     if world > 1:
         dist.barrier()
     torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record(sim.main)
-    sim.run(nt, overlap=overlap)
+    sim.run(nt, overlap=overlap, graph=graph)
     e1.record(sim.main)
     torch.cuda.synchronize()
     us = maxr(e0.elapsed_time(e1)) * 1e3 / nt
-    out[("fast_" if fast else "exact_") + ("overlap_us" if overlap else "serial_us")] = round(us, 2)
+    out[("fast_" if fast else "exact_") + ("overlap" if overlap else "serial") + ("_graph_us" if graph else "_us")] = round(us, 2)
 # stencil alone (no exchange) for reference
 for fast in (False, True):
     sim.fast = fast

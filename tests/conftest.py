@@ -12,7 +12,7 @@ for p in (os.path.join(ROOT, "implicitglobalgrid.jl_b200"), ROOT):
         sys.path.insert(0, p)
 
 
-# Direct-to-halo is taken from 4 MiB of staged data per call by default; the tile-table tests use small arrays, and
+# Direct-to-halo is taken from 32 MiB of staged data per call by default; the tile-table tests use small arrays, and
 # the library reads the variable once per process.
 os.environ.setdefault("IGG_DIRECT_THRESHOLD", "0")
 

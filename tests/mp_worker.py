@@ -337,9 +337,9 @@ def main():
     grids, Ts, Cps, dxyz, dt = D.setup(n, nd)
     T0, Cp0 = Ts[me].copy(order="F"), Cps[me].copy(order="F")
     want = None if quick else D.run(grids, Ts, Cps, dxyz, dt, nt)[me]
-    for overlap in (() if quick else (False, True)):
+    for overlap in (() if quick else (False, True, "graph")):
         sim = Diffusion3D(*nd, T=T0, Cp=Cp0)
-        got = igg.to_numpy(sim.run(nt, overlap=overlap))
+        got = igg.to_numpy(sim.run(nt, overlap=False, graph=True) if overlap == "graph" else sim.run(nt, overlap=overlap))
         sim.finalize()
         if not np.array_equal(got.view(np.uint64), want.view(np.uint64)):
             ok = False

@@ -21,7 +21,7 @@ def test_multirank_vs_oracle(nranks, proto):
     if not torch.cuda.is_available() or torch.cuda.device_count() < nranks:
         pytest.skip(f"needs {nranks} GPUs")
     env = dict(os.environ, MASTER_ADDR="127.0.0.1", IGG_DEVICE_TIMEOUT_S="20", IGG_HOST_TIMEOUT_S="60", IGG_MODE=proto,
-               IGG_DIRECT_THRESHOLD="0")        # direct-to-halo also for the small cases (default: from 4 MiB per call)
+               IGG_DIRECT_THRESHOLD="0")        # direct-to-halo also for the small cases (default: from 32 MiB per call)
     if proto == "auto":
         env["IGG_BULK_THRESHOLD"] = "16384"
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={nranks}",
