@@ -178,12 +178,16 @@ def init_global_grid(nx, ny=1, nz=1, *, dimx=0, dimy=0, dimz=0, periodx=0, perio
     L.check(lib.igg_create(C.byref(g.desc), C.byref(ctx)))
     g.ctx = ctx.value
     if nprocs > 1:
-        n = lib.igg_bootstrap_size()
-        blob = C.create_string_buffer(n)
-        L.check(lib.igg_bootstrap_export(g.ctx, blob))
-        blobs = comm.allgather_bytes(blob.raw)
-        allb = C.create_string_buffer(b"".join(blobs), n * nprocs)
-        L.check(lib.igg_bootstrap_import(g.ctx, allb, nprocs))
+        try:
+            n = lib.igg_bootstrap_size()
+            blob = C.create_string_buffer(n)
+            L.check(lib.igg_bootstrap_export(g.ctx, blob))
+            blobs = comm.allgather_bytes(blob.raw)
+            allb = C.create_string_buffer(b"".join(blobs), n * nprocs)
+            L.check(lib.igg_bootstrap_import(g.ctx, allb, nprocs))
+        except BaseException:
+            lib.igg_destroy(g.ctx)          # a failed bootstrap must not leave a context (and its device memory) behind
+            raise
     _grid = g
     tic()
     toc()

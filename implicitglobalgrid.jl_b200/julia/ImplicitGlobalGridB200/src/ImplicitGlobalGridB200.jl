@@ -15,6 +15,7 @@ import MPI
 
 export init_global_grid, finalize_global_grid, update_halo!, gather!, select_device, get_global_grid
 export nx_g, ny_g, nz_g, x_g, y_g, z_g, ix_g, iy_g, iz_g, tic, toc
+export prepare_update_halo, alloc_field, free_field
 
 const LIB = get(ENV, "IGG_B200_LIB", "libigg_b200.so")
 const NDIMS = 3
@@ -113,7 +114,8 @@ function init_global_grid(nx::Integer, ny::Integer=1, nz::Integer=1; dimx::Integ
     org = Float64[(origin isa Number ? (origin, 0.0, 0.0) : (origin..., 0.0, 0.0)[1:3])...]
     gg = GlobalGrid(nxyz_g, nxyz, dims, collect(overlaps), collect(halowidths), org, origin_on_vertex,
                     [centerx, centery, centerz], nprocs, me, coords, neighbors, periods, comm_cart, quiet, C_NULL)
-    GRID[] = gg
+    GRID[] = gg            # select_device() and tic()/toc() below read it; reset if anything fails (a retry must work)
+    try
     (!quiet && me == 0) && println("Global grid: $(nxyz_g[1])x$(nxyz_g[2])x$(nxyz_g[3]) (nprocs: $nprocs, dims: $(dims[1])x$(dims[2])x$(dims[3]); device support: CUDA (libigg_b200))")
     dev = select_device ? ImplicitGlobalGridB200.select_device() : CUDA.deviceid(CUDA.device())
     nb = ntuple(i -> (v = neighbors[(i - 1) % 2 + 1, (i - 1) ÷ 2 + 1]; Int64(v == MPI.PROC_NULL ? -1 : v)), 6)
@@ -130,6 +132,11 @@ function init_global_grid(nx::Integer, ny::Integer=1, nz::Integer=1; dimx::Integ
         check(ccall((:igg_bootstrap_import, LIB), Cint, (Ptr{Cvoid}, Ptr{UInt8}, Cint), gg.ctx, blobs, nprocs))
     end
     tic(); toc()
+    catch
+        gg.ctx == C_NULL || ccall((:igg_destroy, LIB), Cint, (Ptr{Cvoid},), gg.ctx)
+        GRID[] = nothing
+        rethrow()
+    end
     return me, dims, nprocs, coords, comm_cart
 end
 
@@ -163,14 +170,44 @@ _hw(a::NamedTuple) = Tuple(Int.(a.halowidths))
 _devptr(A::CuArray) = reinterpret(Ptr{Cvoid}, pointer(A))
 _devptr(A::Array) = Ptr{Cvoid}(pointer(A))          # must be page-locked (CUDA.pin / Mem.register); the library rejects pageable memory
 
+# CellArray arguments (CellArrays.jl, loaded by the caller; recognised by their fields, so that this package does not
+# depend on it): as the reference does (ref: src/shared.jl:246-250,287-289), a CellArray with B = 0 contributes one
+# field per cell component (strided component views are copied by nobody: `field(A, i)` of a B = 0 CellArray is a dense
+# N-dimensional array), one with B = 1 a single field whose elements are whole cells; other B are refused.
+_is_cellarray(a) = hasproperty(a, :data) && hasproperty(a, :dims) && !(a isa AbstractArray{<:Number})
+function _bitsarrays(A)
+    T = eltype(A); B = typeof(A).parameters[3]
+    if B == 0
+        ncomp = T <: Number ? 1 : length(T)
+        return [reshape(view(A.data, :, i, 1), size(A)) for i in 1:ncomp]
+    elseif B == 1
+        return [reshape(reinterpret(T, view(A.data, :)), size(A))]
+    end
+    error("only CellArrays with B=0 or B=1 are supported")
+end
+function _extract_all(A::Tuple)
+    out = Any[]
+    for a in A
+        if a isa NamedTuple && _is_cellarray(a.A)
+            append!(out, [(A=b, halowidths=a.halowidths) for b in _bitsarrays(a.A)])
+        elseif _is_cellarray(a)
+            append!(out, _bitsarrays(a))
+        else
+            push!(out, a)
+        end
+    end
+    return Tuple(out)
+end
+
 """
     update_halo!(A...; dims=(3,1,2))
 
 Same call forms as ImplicitGlobalGrid.update_halo!: arrays and/or `(A=array, halowidths=(..))` named tuples.
 One ccall; blocks until the halos are written.
 """
-function update_halo!(A::FieldArg...; dims=(NDIMS, (1:NDIMS-1)...))
+function update_halo!(A...; dims=(NDIMS, (1:NDIMS-1)...))
     gg = grid()
+    A = _extract_all(A)
     arrays = map(_array, A)
     # type-level checks stay on the host side; the rest is checked by the library with the reference's messages
     for (i, a) in enumerate(arrays)
@@ -187,6 +224,32 @@ function update_halo!(A::FieldArg...; dims=(NDIMS, (1:NDIMS-1)...))
     end
     return nothing
 end
+
+# ---- prepared calls and symmetric fields (library extensions, see include/igg_b200.h) ----------------------------
+"`call = prepare_update_halo(A...; dims)`: validates once; `call()` repeats the update with one cheap ccall."
+function prepare_update_halo(A...; dims=(NDIMS, (1:NDIMS-1)...), blocking::Bool=true)
+    gg = grid()
+    A = _extract_all(A)
+    arrays = map(_array, A)
+    fields = [Field(_devptr(a), (size(a, 1), size(a, 2), size(a, 3)), _hw(f), Int32(sizeof(eltype(a))), Int32(ndims(a)))
+              for (a, f) in zip(arrays, A)]
+    d = Cint[dims...]
+    h = Ref{Ptr{Cvoid}}(C_NULL)
+    check(ccall((:igg_prepare, LIB), Cint, (Ptr{Cvoid}, Cint, Ptr{Field}, Ptr{Cint}, Cint, Ref{Ptr{Cvoid}}),
+                gg.ctx, length(fields), fields, d, length(d), h))
+    handle = h[]
+    return () -> (GC.@preserve arrays check(ccall((:igg_update_halo_prepared, LIB), Cint, (Ptr{Cvoid}, Ptr{Cvoid}, Cint),
+                                                   handle, CUDA.stream().handle, blocking ? 0 : 1)); nothing)
+end
+
+"`alloc_field(T, dims...)`: a zeroed CuArray inside a symmetric allocation (collective): update_halo! may store into it from the neighbours directly."
+function alloc_field(::Type{T}, dims::Integer...) where {T}
+    gg = grid()
+    p = Ref{Ptr{Cvoid}}(C_NULL)
+    check(ccall((:igg_alloc_field, LIB), Cint, (Ptr{Cvoid}, Csize_t, Ref{Ptr{Cvoid}}), gg.ctx, prod(dims) * sizeof(T), p))
+    return unsafe_wrap(CuArray, reinterpret(CuPtr{T}, p[]), dims; own=false)
+end
+free_field(A::CuArray) = (check(ccall((:igg_free_field, LIB), Cint, (Ptr{Cvoid}, Ptr{Cvoid}), grid().ctx, _devptr(A))); nothing)
 
 # ---- gather! -----------------------------------------------------------------------------------------------------
 """
