@@ -532,9 +532,11 @@ __device__ __forceinline__ void halo_exchange_body(const KParams& p) {
     // (Launches that exchange with no other rank carry no state: nothing to read, no barrier, no count.)
     unsigned int seen = 0;
     if (p.state && threadIdx.x == 0) seen = atomicAdd(&p.state->blocks_done, 1u);
-    // Let the next kernel of the stream begin its launch now; it cannot touch memory before this grid has completed
-    // (it starts with griddepcontrol.wait, or it is an ordinary launch that waits for completion anyway).
-    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    // Let the next kernel of the stream begin its launch; it cannot touch memory before this grid has completed (it
+    // starts with griddepcontrol.wait, or it is an ordinary launch that waits for completion anyway).  Launches that
+    // exchange with no other rank say so at once; launches whose blocks wait for neighbours only after their tiles
+    // (below), so that an early-scheduled grid does not sit on SM slots while this one is still pushing.
+    if (!p.state) asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     if (p.trace && threadIdx.x == 0)   // [7]: what the block's first tile is (kind, vector width, rows, columns)
         p.trace[(size_t)blockIdx.x * 8 + 7] = (unsigned long long)t.kind | ((unsigned long long)t.vec_log2 << 8) |
                                               ((unsigned long long)t.nrows << 16) | ((unsigned long long)t.ncols << 40);
@@ -664,6 +666,7 @@ __device__ __forceinline__ void halo_exchange_body(const KParams& p) {
         t = get_tile(p, ti);
     }
 
+    if (p.state) asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     if (p.state && threadIdx.x == 0 && seen == gridDim.x - 1) {
         p.state->blocks_done = 0;
         p.state->call_epoch = s_epoch;
@@ -713,8 +716,9 @@ int launch_halo_kernel(const KParams& p, int grid, void* stream, bool ll128) {
     // Programmatic dependent launch: the next grid is scheduled while this one still runs and waits at
     // griddepcontrol.wait, which hides its launch latency.  Default: on for launches that exchange with no other rank
     // (no exchange state to read, nothing to spin on: cfg2 on one GPU 10.3 -> 8.1 us per stream-ordered call, 8.8 ->
-    // 7.9 us replayed from a graph), off for launches whose blocks wait for a neighbour (an early-scheduled grid takes
-    // SM slots from a grid that is still pushing: measured slower in round 1).  IGG_PDL=1 / 0 forces it on / off.
+    // 7.9 us replayed from a graph), off for launches whose blocks wait for a neighbour: measured slower per
+    // stream-ordered call on 2 GPUs whether the dependents are released in the prologue (14.1 vs 13.0 us) or after
+    // the tiles (14.4 vs 13.2 us; replayed from a graph 10.1 vs 10.5 us).  IGG_PDL=1 / 0 forces it on / off.
     static const int pdl_env = [] { const char* e = getenv("IGG_PDL"); return !e ? -1 : (e[0] == '1' ? 1 : 0); }();
     const bool pdl = pdl_env >= 0 ? pdl_env == 1 : p.state == nullptr;
     cudaLaunchConfig_t cfg = {};
