@@ -1,7 +1,8 @@
 """Randomised check of the tile tables (hypothesis): for random process grids, periodicities, overlaps, halowidths,
-field shapes (staggered up and down), element sizes, pointer alignments and `dims=` orders, the tile tables of both
-IPC protocols -- executed on the CPU as the kernels address memory (tests/test_tiles_cpu.py) -- give exactly what
-the oracle's three dependent phases give.  No GPU needed."""
+field shapes (staggered up and down, narrow and wide in x), element sizes, pointer alignments and `dims=` orders,
+with and without symmetric fields (direct-to-halo), the tile tables of both IPC protocols -- executed on the CPU as
+the kernels address memory (tests/test_tiles_cpu.py) -- give exactly what the oracle's three dependent phases give.
+No GPU needed."""
 import numpy as np
 from hypothesis import HealthCheck, given, settings, strategies as st
 
@@ -19,6 +20,8 @@ def configs(draw):
     hw = [draw(st.integers(1, 3)) if d < ndim else 1 for d in range(3)]
     ol = [draw(st.integers(2 * hw[d], 2 * hw[d] + 2)) if d < ndim else 2 for d in range(3)]
     n = [draw(st.integers(ol[d] + 2 * hw[d] + 1, ol[d] + 2 * hw[d] + 7)) if d < ndim else 1 for d in range(3)]
+    if draw(st.booleans()):
+        n[0] += 128          # rows of 1 KiB and more (with 8-byte elements): wide enough for direct-to-halo
     nf = draw(st.integers(1, 3))
     shapes = []
     for _ in range(nf):
@@ -31,8 +34,8 @@ def configs(draw):
 
 
 @settings(max_examples=60, deadline=None, suppress_health_check=[HealthCheck.too_slow, HealthCheck.data_too_large])
-@given(configs(), st.sampled_from([L.IGG_MODE_IPC_1PHASE, L.IGG_MODE_IPC_LL128]))
-def test_random_tile_tables_match_oracle(cfg, mode):
+@given(configs(), st.sampled_from([L.IGG_MODE_IPC_1PHASE, L.IGG_MODE_IPC_LL128, L.IGG_MODE_IPC_AUTO]), st.booleans())
+def test_random_tile_tables_match_oracle(cfg, mode, direct):
     dims, periods, hw, ol, n, shapes, elsize, order, seed = cfg
     nprocs = dims[0] * dims[1] * dims[2]
     try:
@@ -49,7 +52,8 @@ def test_random_tile_tables_match_oracle(cfg, mode):
     except O.IGGError:
         return                                           # e.g. a field without any halo: rejected by check_fields
     got = [[a.copy(order="F") for a in fr] for fr in base]
-    run_tables(grids, got, hws, order, mode)
+    auto = mode == L.IGG_MODE_IPC_AUTO                    # (small calls: auto = LL128 tiles)
+    run_tables(grids, got, hws, order, L.IGG_MODE_IPC_LL128 if auto else mode, direct=direct)
     for r in range(nprocs):
         for i in range(len(shapes)):
             assert np.array_equal(flat_bytes(got[r][i]), flat_bytes(want[r][i])), (r, i)
