@@ -201,12 +201,19 @@ def main():
             igg.gather(A, G, root=root)
             blocks = [None] * n
             dist.all_gather_object(blocks, igg.to_numpy(A))
+            # the same into page-locked HOST memory on root: A_global cannot be exported over CUDA IPC, so the blocks go
+            # through the context's device image of A_global and root copies it out (the path kept for such memory)
+            GH = igg.zeros(tuple(s * d for s, d in zip(A.shape, dimsg)), dtype=A.dtype, pin_memory=True) if me == root else None
+            igg.gather(A, GH, root=root)
             if me == root:
                 wantG = np.zeros(tuple(G.shape), dtype=blocks[0].dtype, order="F")
                 O.gather(grids, blocks, wantG, root=root)
                 if not np.array_equal(igg.to_numpy(G), wantG):
                     ok = False
                     print(f"GATHER MISMATCH case {ci} root {root}", flush=True)
+                if not np.array_equal(igg.to_numpy(GH), wantG):
+                    ok = False
+                    print(f"GATHER (host A_global) MISMATCH case {ci} root {root}", flush=True)
         igg.finalize_global_grid()
         dist.barrier()
     # Calls with different field sets and `dims=` alternating on ONE context: every neighbour offset keeps its own
