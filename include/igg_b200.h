@@ -23,7 +23,7 @@
 extern "C" {
 #endif
 
-#define IGG_VERSION 100          /* 0.1.0 */
+#define IGG_VERSION 200          /* 0.2.0: prepared calls, symmetric fields, IGG_MODE_IPC_AUTO */
 #define IGG_PROC_NULL (-1)       /* stand-in for MPI.PROC_NULL in igg_grid_desc.neighbors */
 #define IGG_MAX_FIELDS 32        /* fields per update_halo call */
 #define IGG_NOFFSETS 27          /* neighbour offsets (-1,0,1)^3, index = (ox+1) + 3*(oy+1) + 9*(oz+1) */

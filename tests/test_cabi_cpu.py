@@ -27,7 +27,7 @@ def test_library_exports_every_declared_symbol():
     for name in sorted(declared):
         assert hasattr(lib, name), f"libigg_b200.so does not export {name}"
     assert declared == set(L.DECLARED_SYMBOLS), declared ^ set(L.DECLARED_SYMBOLS)
-    assert lib.igg_version() == 100
+    assert lib.igg_version() == 200
     want = b"igg_halo_exchange_kernel" if os.environ.get("IGG_MODE") in ("fence", "ipc") else b"igg_halo_exchange_ll128_kernel"
     assert lib.igg_kernel_name() == want
     assert lib.igg_bootstrap_size() == 256
