@@ -128,6 +128,7 @@ struct igg_ctx {
     // polled where LL128 lines are written, so payload of the other protocol cannot be mistaken for an epoch word.
     int64_t  region_cap[2][IGG_NOFFSETS] = {{0}}, region_off[2][IGG_NOFFSETS] = {{0}};
     uint32_t flag_cap[IGG_NOFFSETS] = {0}, flag_off[IGG_NOFFSETS] = {0};
+    char* hostx_cache = nullptr; int64_t hostx_cache_cap = 0;     // row-end lines of host-resident fields (exchanged x-faces)
     cudaStream_t side_stream = nullptr;         // host-resident fields: the wrap-lines kernel runs beside the exchange
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     unsigned long long timeout_ns = 20ull * 1000000000ull;
@@ -421,6 +422,11 @@ static Plan* find_or_build_plan(igg_ctx* ctx, int nfields, const igg_field* fiel
         if (e == cudaSuccess) e = upload_now(plan->d_wrap_tiles, plan->wrap_tiles.data(), plan->wrap_tiles.size() * sizeof(TileRec));
         if (e != cudaSuccess) { cudaFree(plan->d_plan); *rc_out = fail(IGG_ERR_CUDA, "plan upload failed: %s", cudaGetErrorString(e)); return nullptr; }
     }
+    if (!plan->hostx_tiles.empty()) {
+        cudaError_t e = cudaMalloc(&plan->d_hostx_tiles, plan->hostx_tiles.size() * sizeof(TileRec));
+        if (e == cudaSuccess) e = upload_now(plan->d_hostx_tiles, plan->hostx_tiles.data(), plan->hostx_tiles.size() * sizeof(TileRec));
+        if (e != cudaSuccess) { cudaFree(plan->d_plan); cudaFree(plan->d_wrap_tiles); *rc_out = fail(IGG_ERR_CUDA, "plan upload failed: %s", cudaGetErrorString(e)); return nullptr; }
+    }
     // Bound the cache (fields of ever-changing shapes): drop the oldest plan that nothing can still refer to.  Plans
     // behind a prepared call, or launched while their stream was being captured into a CUDA graph, are never dropped.
     if (ctx->plans.size() >= 256) {
@@ -429,6 +435,7 @@ static Plan* find_or_build_plan(igg_ctx* ctx, int nfields, const igg_field* fiel
             cudaDeviceSynchronize();
             cudaFree(ctx->plans[k]->d_plan);
             cudaFree(ctx->plans[k]->d_wrap_tiles);
+            cudaFree(ctx->plans[k]->d_hostx_tiles);
             ctx->plans.erase(ctx->plans.begin() + (long)k);
             break;
         }
@@ -619,7 +626,8 @@ int igg_destroy(igg_ctx* ctx) {
     nccl_free(ctx->nccl);
     ctx->nccl = nullptr;
     for (auto& p : ctx->peers) { close_segment(p.ctrl); close_segment(p.staging); close_segment(p.gather); }
-    for (auto& pl : ctx->plans) { cudaFree(pl->d_plan); cudaFree(pl->d_wrap_tiles); }
+    for (auto& pl : ctx->plans) { cudaFree(pl->d_plan); cudaFree(pl->d_wrap_tiles); cudaFree(pl->d_hostx_tiles); }
+    if (ctx->hostx_cache) cudaFree(ctx->hostx_cache);
     for (auto& reg : ctx->regs) { for (auto& ps : reg.peer) close_segment(ps); }
     if (ctx->g.nprocs > 1 && ctx->cp.attached() && !ctx->regs.empty()) ctx->cp.barrier();   // mappings closed before the frees
     for (auto& reg : ctx->regs) if (reg.base) cudaFree(reg.base);
@@ -886,13 +894,30 @@ static int launch_plan(igg_ctx* ctx, Plan* plan, int nfields, const igg_field* f
     for (int i = 0; i < nfields; ++i) p.field[i] = fields[i].ptr;
     for (int i = nfields; i < IGG_MAX_FIELDS; ++i) p.field[i] = nullptr;
     order_after_previous(ctx, stream);
+    const bool hostx = !plan->hostx_tiles.empty();
+    void* host_ptrs[IGG_MAX_FIELDS];
+    if (hostx) {
+        // Exchanged x-faces of host-resident fields: fetch the row-end lines into the device cache; the exchange
+        // kernel sees every such field's lines as one more field (index nfields + k).
+        if (plan->hostx_cache_bytes > ctx->hostx_cache_cap) {
+            CU(cudaDeviceSynchronize());
+            if (ctx->hostx_cache) { CU(cudaFree(ctx->hostx_cache)); ctx->hostx_cache = nullptr; }
+            CU(cudaMalloc(&ctx->hostx_cache, (size_t)plan->hostx_cache_bytes));
+            ctx->hostx_cache_cap = plan->hostx_cache_bytes;
+        }
+        for (int i = 0; i < nfields; ++i) host_ptrs[i] = fields[i].ptr;
+        rc = launch_host_lines_kernel(plan->d_hostx_tiles, (int)plan->hostx_tiles.size(), host_ptrs, nfields, ctx->hostx_cache, false, stream);
+        if (rc) return rc;
+        ctx->launches += 1;
+        for (size_t k = 0; k < plan->hostx.size(); ++k) p.field[nfields + (int)k] = ctx->hostx_cache + plan->hostx[k].cache_off;
+    }
     if (ctx->d_trace) {
         p.trace = ctx->d_trace;
         ctx->last_grid = plan->grid;
         CU(cudaMemsetAsync(ctx->d_trace, 0, (size_t)ctx->max_blocks * 8 * sizeof(unsigned long long), stream));
     }
     unsigned long long ticket = 0;
-    if (sync && ctx->spin_wait && !join_side) {
+    if (sync && ctx->spin_wait && !join_side && !hostx) {
         ticket = ++ctx->ticket;
         p.notify = ctx->d_done;
         p.notify_value = ticket;
@@ -901,6 +926,11 @@ static int launch_plan(igg_ctx* ctx, Plan* plan, int nfields, const igg_field* f
     if (join_side) CU(cudaStreamWaitEvent(stream, ctx->ev_join, 0));   // the call is complete when both kernels are
     if (rc) return rc;
     remember_launch(ctx, stream);
+    if (hostx) {                                   // the cached lines, halos patched, go back to the host whole
+        rc = launch_host_lines_kernel(plan->d_hostx_tiles, (int)plan->hostx_tiles.size(), host_ptrs, nfields, ctx->hostx_cache, true, stream);
+        if (rc) return rc;
+        ctx->launches += 1;
+    }
     if (ticket) {
         *waited = true;
         return wait_done(ctx, stream, ticket);

@@ -253,6 +253,31 @@ __global__ void __launch_bounds__(kThreads) igg_wrap_lines_kernel(const TileRec*
     }
 }
 
+// kOpHostLinesX (fields in page-locked host memory whose x-faces go to another rank): copies the first and the last
+// 64-byte line of `nrows` rows between the host field and a device cache (128 bytes per row: first line, last line).
+// Eight lanes own a row (lanes 0-3 the first line, 4-7 the last), so every line is one 64-byte PCIe request in either
+// direction and no partial write reaches the host's memory controller.  WRITE_BACK = false: host -> cache, in front of
+// the exchange kernel; true: cache -> host, behind it.  Only the ends that are exchanged (t.dst_sz) are touched.
+template <bool WRITE_BACK>
+__global__ void __launch_bounds__(kThreads) igg_host_lines_kernel(const TileRec* __restrict__ tiles, const __grid_constant__ WrapFields f,
+                                                                  char* __restrict__ cache) {
+    const TileRec t = load_tile(tiles + blockIdx.x);
+    char* rows = static_cast<char*>(f.field[t.field]) + t.src_off;
+    const int64_t sy = t.src_sy, sz = t.src_sz, pitch = t.dst_off;
+    const uint32_t sides = (uint32_t)t.dst_sz, ny = t.ny;
+    uint4* lines = reinterpret_cast<uint4*>(cache + t.dst_sy);
+    for (uint32_t i = threadIdx.x; i < t.nrows * 8u; i += kThreads) {
+        const uint32_t row = t.row0 + (i >> 3), j = i & 7u;
+        if (!((sides >> (j >> 2)) & 1u)) continue;
+        uint32_t z = 0, y = row;
+        if (row >= ny) { z = row / ny; y = row - z * ny; }
+        uint4* host = reinterpret_cast<uint4*>(rows + (int64_t)y * sy + (int64_t)z * sz + (j < 4 ? 0 : pitch - 128)) + j;
+        uint4* dev = lines + (size_t)row * 8 + j;
+        if (WRITE_BACK) *host = *dev;
+        else *dev = *host;
+    }
+}
+
 // ---- bulk-copy pipeline (fence kernel): global -> shared -> global with cp.async.bulk (TMA unit) ------------------
 // For tiles of long contiguous rows (the y/z faces of the bandwidth regime: 2 KiB - 512 KiB runs) one thread of the
 // block moves the tile through a ring of shared-memory stages: bulk loads complete on an mbarrier per stage, bulk
@@ -744,6 +769,18 @@ int launch_wrap_lines_kernel(const TileRec* d_tiles, int n_tiles, void* const* f
     igg_wrap_lines_kernel<<<n_tiles, kThreads, 0, static_cast<cudaStream_t>(stream)>>>(d_tiles, f);
     const cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return fail(IGG_ERR_CUDA, "wrap-lines kernel launch failed: %s", cudaGetErrorString(e));
+    return IGG_OK;
+}
+
+int launch_host_lines_kernel(const TileRec* d_tiles, int n_tiles, void* const* fields, int nfields, char* cache,
+                             bool write_back, void* stream) {
+    WrapFields f;
+    std::memset(&f, 0, sizeof(f));
+    for (int i = 0; i < nfields && i < IGG_MAX_FIELDS; ++i) f.field[i] = fields[i];
+    if (write_back) igg_host_lines_kernel<true><<<n_tiles, kThreads, 0, static_cast<cudaStream_t>(stream)>>>(d_tiles, f, cache);
+    else igg_host_lines_kernel<false><<<n_tiles, kThreads, 0, static_cast<cudaStream_t>(stream)>>>(d_tiles, f, cache);
+    const cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return fail(IGG_ERR_CUDA, "host-lines kernel launch failed: %s", cudaGetErrorString(e));
     return IGG_OK;
 }
 

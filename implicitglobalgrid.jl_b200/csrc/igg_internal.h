@@ -139,6 +139,15 @@ struct FieldKey {
     bool operator==(const FieldKey& o) const { return std::memcmp(this, &o, sizeof(*this)) == 0; }
 };
 
+// A page-locked host field whose x-faces are exchanged through a device cache of its row-end lines (plan.cpp).
+struct HostXField {
+    int      field = 0;                    // index into the call's field list; the cache is field nfields + k of the launch
+    int64_t  rows = 0, ny = 0;             // rows of the x-face box (ny per plane)
+    int64_t  cache_off = 0;                // byte offset of this field's lines in the context's cache (128 B per row)
+    int64_t  row_org = 0, pitch = 0, plane = 0;   // first row of the box in the host field, byte strides
+    uint32_t sides = 0;                    // bit 0: low end exchanged, bit 1: high end
+};
+
 struct Plan {
     std::vector<FieldKey>    key;
     int                      dims_mask = 0;          // bit d set: dimension d (0..2) is updated
@@ -174,6 +183,11 @@ struct Plan {
     // kOpWrapX tiles: where they are in `tiles` and the per-op descriptors they were cut from
     int32_t  wx_first = 0, wx_count = 0;
     std::vector<WrapXOp>     wx_ops;
+    // exchanged x-faces of host-resident fields: cached lines (kOpHostLinesX tiles: fetched before, written back after)
+    std::vector<HostXField>  hostx;
+    std::vector<TileRec>     hostx_tiles;
+    TileRec* d_hostx_tiles = nullptr;
+    int64_t  hostx_cache_bytes = 0;
     // kOpWrapLines tiles of host-resident fields (run by igg_wrap_lines_kernel, one block each)
     std::vector<TileRec>     wrap_tiles;
     TileRec* d_wrap_tiles = nullptr;
@@ -213,6 +227,11 @@ constexpr int kOpCopyIn = 4; // internal tile kind: unpack_base[t.nbr] -> field[
 // TileRec use: src_off/src_sy/src_sz/row0/nrows/ny address the rows (x = 0); dst_off = row pitch in bytes,
 // dst_sy = halo width in bytes, dst_sz = overlap in bytes (<= 64); ncols = 8 lanes per row.
 constexpr int kOpWrapLines = 5;
+// Exchanged x-faces of page-locked HOST fields: one tile = up to kWrapRowsPerTile rows whose first and last 64-byte
+// line are copied into / out of a device cache (128 bytes per row) by igg_host_lines_kernel.  TileRec use: src_off /
+// src_sy / src_sz / row0 / nrows / ny address the rows in the host field, dst_off = row pitch, dst_sy = byte offset of
+// the field's lines in the cache, dst_sz = sides (bit 0 low end, bit 1 high end).
+constexpr int kOpHostLinesX = 11;
 constexpr int kWrapRowsPerTile = 128;
 // IGG_MODE_IPC_LL128: PUSH / UNPACK through line-formatted staging.  A staging slot of n payload bytes is
 // ceil(n / 120) lines of 128 bytes: bytes [0,120) payload (the box in column-major order, as a stream of W-byte
@@ -271,5 +290,8 @@ int  launch_halo_kernel(const KParams& p, int grid, void* stream, bool ll128 = f
 const char* halo_kernel_name();
 // kOpWrapLines tiles (host-resident fields), one block per tile, stream-ordered.
 int  launch_wrap_lines_kernel(const TileRec* d_tiles, int n_tiles, void* const* fields, int nfields, void* stream);
+// kOpHostLinesX tiles: host lines -> cache (write_back = false) or cache -> host lines (true), one block per tile.
+int  launch_host_lines_kernel(const TileRec* d_tiles, int n_tiles, void* const* fields, int nfields, char* cache,
+                              bool write_back, void* stream);
 
 }  // namespace igg

@@ -412,6 +412,24 @@ int build_plan(const igg_grid_desc& g, int nfields, const igg_field* fields, int
     std::vector<igg_plan_op> push, local, unpack;
     std::vector<TileRec> tpush, twrapx, tlocal, tunpack;
 
+    // Host-resident fields whose x-faces go to another rank through cached whole lines (see the op loop): index into
+    // plan.hostx or -1.  IGG_HOST_LINES_X=0 keeps the per-cell path.
+    std::vector<int> hostx(nfields, -1);
+    plan.hostx.clear();
+    plan.hostx_cache_bytes = 0;
+    static const bool hostx_on = !(getenv("IGG_HOST_LINES_X") && atoi(getenv("IGG_HOST_LINES_X")) == 0);
+    for (int i = 0; i < nfields && hostx_on; ++i) {
+        const igg_field& f = fields[i];
+        const int64_t el = f.elsize, pitch = f.size[0] * el;
+        if (host_lines && host_lines[i] && g.dims[0] > 1 && halo[i][0] && pitch % 64 == 0 && pitch >= 128 && 64 % el == 0 &&
+            field_ol(g, f, 0) * el <= 64 && nfields + (int)plan.hostx.size() < IGG_MAX_FIELDS) {
+            hostx[i] = (int)plan.hostx.size();
+            HostXField hx;
+            hx.field = i;
+            plan.hostx.push_back(hx);
+        }
+    }
+
     for (int oi = 0; oi < IGG_NOFFSETS; ++oi) {
         int o[3];
         index_offset(oi, o);
@@ -582,6 +600,44 @@ int build_plan(const igg_grid_desc& g, int nfields, const igg_field* fields, int
                     unpack.push_back(up);
                     continue;
                 }
+                // Page-locked HOST field, pure x offset to another rank: the strided cells of the x-face are not read
+                // and written one by one over PCIe (a partial write costs the host a read-modify-write).  A kernel in
+                // front of the exchange fetches the first and the last 64-byte line of every row of the box into a
+                // device cache (kOpHostLinesX tiles), the exchange packs from / unpacks into that cache -- to the
+                // tiles it is one more field: 128 bytes per row, the row's two lines side by side --, and a kernel
+                // behind it writes the lines back whole.  No other op of the call touches these lines (the y/z faces
+                // write y/z halo rows only; the edges and corners keep the per-cell path).
+                const igg_field* kf = &f;
+                igg_field fc;
+                int kidx = i;
+                Box ksnd = snd, krcv = rcv_mine;
+                if (hostx[i] >= 0 && o[0] && !o[1] && !o[2]) {
+                    HostXField& hx = plan.hostx[(size_t)hostx[i]];
+                    const int64_t el = f.elsize, cpl = 128 / el;      // cells in the two cached lines of a row
+                    if (hx.rows == 0) {                               // first x op of this field: lay its cache out
+                        const int64_t pitch = f.size[0] * el;
+                        hx.ny = snd.hi[1] - snd.lo[1] + 1;
+                        hx.rows = hx.ny * (snd.hi[2] - snd.lo[2] + 1);
+                        hx.cache_off = plan.hostx_cache_bytes;
+                        plan.hostx_cache_bytes += hx.rows * 128;
+                        hx.row_org = (snd.lo[1] - 1) * pitch + (snd.lo[2] - 1) * pitch * f.size[1];
+                        hx.pitch = pitch;
+                        hx.plane = pitch * f.size[1];
+                    }
+                    hx.sides |= o[0] < 0 ? 1u : 2u;
+                    fc = f;
+                    fc.ptr = nullptr;                                 // (the cache rows are 128-byte aligned)
+                    fc.size[0] = cpl; fc.size[1] = hx.ny; fc.size[2] = hx.rows / hx.ny;
+                    kf = &fc;
+                    kidx = nfields + hostx[i];
+                    const int64_t shift = o[0] < 0 ? 0 : cpl - f.size[0];     // the high end of the row lives in the second line
+                    ksnd.lo[0] = snd.lo[0] + shift; ksnd.hi[0] = snd.hi[0] + shift;
+                    krcv.lo[0] = rcv_mine.lo[0] + shift; krcv.hi[0] = rcv_mine.hi[0] + shift;
+                    for (int d = 1; d < 3; ++d) {
+                        ksnd.hi[d] = snd.hi[d] - snd.lo[d] + 1; ksnd.lo[d] = 1;
+                        krcv.hi[d] = rcv_mine.hi[d] - rcv_mine.lo[d] + 1; krcv.lo[d] = 1;
+                    }
+                }
                 if (ll128) {
                     // Same boxes, line-formatted staging: the op descriptions keep the field-side geometry (merged
                     // rows and strides); the tiles are runs of staging lines.
@@ -596,12 +652,12 @@ int build_plan(const igg_grid_desc& g, int nfields, const igg_field* fields, int
                             t.ny = (uint32_t)d.ny; t.ncols = (uint32_t)d.row_bytes;
                             t.row0 = (uint32_t)l0; t.nrows = (uint32_t)std::min<int64_t>(kLinesPerTile, nlines - l0);
                             t.dst_off = d.staging_off; t.dst_sy = d.nbytes;
-                            t.field = (uint16_t)i; t.vec_log2 = (uint8_t)wlog; t.kind = (uint8_t)kind; t.nbr = (uint8_t)oi;
+                            t.field = (uint16_t)kidx; t.vec_log2 = (uint8_t)wlog; t.kind = (uint8_t)kind; t.nbr = (uint8_t)oi;
                             out.push_back(t);
                         }
                     };
                     std::vector<TileRec> unused;
-                    lower_op(f, i, IGG_OP_PUSH, oi, snd, snd, true, false, op.staging_off, op, unused);
+                    lower_op(*kf, kidx, IGG_OP_PUSH, oi, ksnd, ksnd, true, false, op.staging_off, op, unused);
                     op.flag_base = -1;
                     emit_ll(kOpPushLL, op.src_off, op.src_sy, op.src_sz, op, tpush);
                     push.push_back(op);
@@ -620,13 +676,13 @@ int build_plan(const igg_grid_desc& g, int nfields, const igg_field* fields, int
                     up.staging_off = slot_off[(size_t)oi * nfields + i];
                     up.flag_base = -1;
                     unused.clear();
-                    lower_op(f, i, IGG_OP_UNPACK, oi, rcv_mine, rcv_mine, false, true, up.staging_off, up, unused);
+                    lower_op(*kf, kidx, IGG_OP_UNPACK, oi, krcv, krcv, false, true, up.staging_off, up, unused);
                     emit_ll(kOpUnpackLL, up.dst_off, up.dst_sy, up.dst_sz, up, tunpack);
                     unpack.push_back(up);
                     continue;
                 }
                 const size_t first_push = tpush.size();
-                lower_op(f, i, IGG_OP_PUSH, oi, snd, snd, true, false, op.staging_off, op, tpush, tb);
+                lower_op(*kf, kidx, IGG_OP_PUSH, oi, ksnd, ksnd, true, false, op.staging_off, op, tpush, tb);
                 if (tpush.size() - first_push > slot_nflag[(size_t)opposite_index(oi) * nfields + i])
                     return fail(IGG_ERR_STATE, "internal: an exchange op has more tiles than its slot has arrival flags.");
                 for (size_t k = first_push; k < tpush.size(); ++k)      // flag numbers in the RECEIVER's slot table
@@ -648,7 +704,7 @@ int build_plan(const igg_grid_desc& g, int nfields, const igg_field* fields, int
                 }
                 up.staging_off = slot_off[(size_t)oi * nfields + i];
                 const size_t first_unpack = tunpack.size();
-                lower_op(f, i, IGG_OP_UNPACK, oi, rcv_mine, rcv_mine, false, true, up.staging_off, up, tunpack, tb);
+                lower_op(*kf, kidx, IGG_OP_UNPACK, oi, krcv, krcv, false, true, up.staging_off, up, tunpack, tb);
                 for (size_t k = first_unpack; k < tunpack.size(); ++k)
                     tunpack[k].flag_idx = slot_flag[(size_t)oi * nfields + i] + (uint32_t)(k - first_unpack);
                 up.flag_base = (int32_t)slot_flag[(size_t)oi * nfields + i];
@@ -670,6 +726,18 @@ int build_plan(const igg_grid_desc& g, int nfields, const igg_field* fields, int
     plan.wx_count = (int32_t)twrapx.size();
     plan.tiles.insert(plan.tiles.end(), twrapx.begin(), twrapx.end());
     plan.tiles.insert(plan.tiles.end(), tunpack.begin(), tunpack.end());
+    plan.hostx_tiles.clear();
+    for (const HostXField& hx : plan.hostx)
+        for (int64_t r0 = 0; r0 < hx.rows; r0 += kWrapRowsPerTile) {
+            TileRec t;
+            std::memset(&t, 0, sizeof(t));
+            t.src_off = hx.row_org; t.src_sy = hx.pitch; t.src_sz = hx.plane;
+            t.dst_off = hx.pitch; t.dst_sy = hx.cache_off; t.dst_sz = hx.sides;
+            t.row0 = (uint32_t)r0; t.nrows = (uint32_t)std::min<int64_t>(kWrapRowsPerTile, hx.rows - r0);
+            t.ncols = 8; t.ny = (uint32_t)hx.ny;
+            t.field = (uint16_t)hx.field; t.vec_log2 = 4; t.kind = (uint8_t)kOpHostLinesX;
+            plan.hostx_tiles.push_back(t);
+        }
     plan.has_bulk = false;           // the LL128 kernel only takes the LOCAL ones through the pipeline
     for (const TileRec& t : plan.tiles) plan.has_bulk = plan.has_bulk || (t.bulk && (!ll128 || t.kind == IGG_OP_LOCAL));
     return IGG_OK;
