@@ -518,7 +518,7 @@ def run_b200(args):
         "e2e": {"value": world * B_send / e2e_sec / 1e9, "unit": UNIT, "us_per_step": e2e_sec * 1e6,
                 "h2d_bytes_per_step": B_send, "d2h_bytes_per_step": B_send, "steps": e2e_steps,
                 "path": "blocking igg_update_halo on fields in pinned host memory; the kernels read the send boxes and "
-                        "write the halos over PCIe (zero-copy; x self-wraps through whole 64-byte lines), no "
+                        "write the halos over PCIe (zero-copy; x-faces, wrapped or exchanged, through whole 64-byte lines), no "
                         "device-resident copy of the field"},
         "per_call_us": dict(per_call_us, n=K, how="SURVEY 8d's per-call figure: one CUDA-event pair around every stream-ordered call (not graph-replayed), loop issued from C, max over ranks; includes the two timing events (~2.5 us each on the stream)"),
         "per_call_python_us": dict(per_call_python_us, n=200, how="the same with CPython in the loop (torch events + ctypes call)"),
