@@ -845,19 +845,26 @@ int igg_plan_tiles(const igg_grid_desc* desc, int nfields, const igg_field* fiel
                    int64_t* regions_out) {
     if (!desc || !fields || !ntiles_out) return igg::fail(IGG_ERR_ARG, "igg_plan_tiles: NULL argument.");
     const bool all_direct = (mode & 0x100) != 0;      // + 0x100: every field lives in a symmetric allocation
+    const bool all_host = (mode & 0x200) != 0;        // + 0x200: every field is page-locked host memory on a 64-byte boundary
     mode &= 0xff;
     if (mode != IGG_MODE_IPC_1PHASE && mode != IGG_MODE_IPC_LL128 && mode != IGG_MODE_IPC_AUTO)
         return igg::fail(IGG_ERR_ARG, "igg_plan_tiles: mode must be an IPC mode.");
     uint8_t direct[IGG_MAX_FIELDS];
     std::memset(direct, all_direct ? 1 : 0, sizeof(direct));
+    uint8_t host[IGG_MAX_FIELDS];                       // + 0x200 (before masking): every field is page-locked host memory
+    std::memset(host, all_host ? 1 : 0, sizeof(host));
     int mask;
     int rc = igg::dims_mask_from_order(dims_order, ndims_order, &mask);
     if (rc) return rc;
     igg::Plan plan;
-    rc = igg::build_plan(*desc, nfields, fields, mask, plan, nullptr,
+    rc = igg::build_plan(*desc, nfields, fields, mask, plan, all_host ? host : nullptr,
                          mode == IGG_MODE_IPC_LL128 ? igg::kProtoLL128 : mode == IGG_MODE_IPC_AUTO ? igg::kProtoAuto : igg::kProtoFence,
                          direct);
     if (rc) return rc;
+    // host fields: the whole-line tiles (x self-wraps: kind 5; fetch / write-back of exchanged x-faces: kind 11) follow
+    // the exchange kernel's table
+    plan.tiles.insert(plan.tiles.end(), plan.wrap_tiles.begin(), plan.wrap_tiles.end());
+    plan.tiles.insert(plan.tiles.end(), plan.hostx_tiles.begin(), plan.hostx_tiles.end());
     *ntiles_out = (int)plan.tiles.size();
     if (staging_bytes_out) *staging_bytes_out = plan.staging_bytes;
     if (regions_out)

@@ -245,7 +245,10 @@ int igg_plan_describe(const igg_grid_desc* desc, int nfields, const igg_field* f
  * on this rank: `*ntiles_out` records of 80 bytes each (layout: struct TileRec in csrc/igg_internal.h; PUSH tiles
  * first, then the LOCAL tiles and the x self-wraps (WRAPX), then UNPACK).  `mode` may also be
  * IGG_MODE_IPC_AUTO; adding 0x100 to it treats every field as living in a symmetric allocation (igg_alloc_field):
- * boxes that span x then go straight into the neighbour's field (PUSH_DIRECT tiles) and the receiver only waits.  `regions_out` (may be NULL) receives 4 x 27 numbers, indexed by neighbour offset
+ * boxes that span x then go straight into the neighbour's field (PUSH_DIRECT tiles) and the receiver only waits.
+ * Adding 0x200 treats every field as page-locked host memory on a 64-byte boundary: the table is then followed by the
+ * whole-line tiles the host-field kernels run (kind 5: x self-wraps; kind 11: fetch / write-back of the row-end lines
+ * of x-faces that go to another rank, whose cache the exchange tiles address as fields nfields, nfields + 1, ...).  `regions_out` (may be NULL) receives 4 x 27 numbers, indexed by neighbour offset
  * (ox+1) + 3(oy+1) + 9(oz+1): where that offset's staging slots start in the table's packed layout, how many bytes
  * of a staging half the offset needs, and the same two for its arrival flags.  (At run time every offset owns a
  * region whose position does not depend on the call; the launch shifts each offset's base accordingly.)

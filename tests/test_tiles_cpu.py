@@ -14,6 +14,7 @@ from oracle import igg_oracle as O
 from test_plan_vs_oracle import desc_of, flat_bytes, rand_field
 
 PUSH, LOCAL, UNPACK, PUSH_LL, UNPACK_LL, WRAPX, PUSH_DIRECT, WAIT = 0, 1, 2, 6, 7, 8, 9, 10
+WRAP_LINES, HOST_LINES_X = 5, 11
 LINE, PAYLOAD = 128, 120
 OFFSETS = [(ox, oy, oz) for oz in (-1, 0, 1) for oy in (-1, 0, 1) for ox in (-1, 0, 1)]   # index = (ox+1)+3(oy+1)+9(oz+1)
 
@@ -57,6 +58,33 @@ def wrap_x(t, mem):
             mem[lo_send - delta:lo_send - delta + W] = b
 
 
+def wrap_lines(t, mem):
+    """igg_wrap_lines_kernel: periodic x self-wrap of host rows through their first and last 64-byte line."""
+    hwb, olb, pitch = t.dst_sy, t.dst_sz, t.dst_off
+    for r in range(t.nrows):
+        row = t.row0 + r
+        y, z = row % t.ny, row // t.ny
+        a = t.src_off + y * t.src_sy + z * t.src_sz
+        L = np.concatenate([mem[a:a + 64], mem[a + pitch - 64:a + pitch]])
+        L[0:hwb], L[128 - hwb:128] = L[128 - olb:128 - olb + hwb].copy(), L[olb - hwb:olb].copy()
+        mem[a:a + 64], mem[a + pitch - 64:a + pitch] = L[:64], L[64:]
+
+
+def host_lines(t, mem, cache, write_back):
+    """igg_host_lines_kernel: first / last 64-byte line of every row <-> 128 bytes per row of the device cache."""
+    pitch, sides = t.dst_off, t.dst_sz
+    for r in range(t.nrows):
+        row = t.row0 + r
+        y, z = row % t.ny, row // t.ny
+        a, c = t.src_off + y * t.src_sy + z * t.src_sz, t.dst_sy + row * 128
+        for side, (h, d) in enumerate(((a, c), (a + pitch - 64, c + 64))):
+            if (sides >> side) & 1:
+                if write_back:
+                    mem[h:h + 64] = cache[d:d + 64]
+                else:
+                    cache[d:d + 64] = mem[h:h + 64]
+
+
 def box_offset(t, pb):
     """box_seek of the kernel: payload byte pb -> byte offset in the field."""
     r, c = divmod(pb, t.ncols)
@@ -64,15 +92,30 @@ def box_offset(t, pb):
     return t.src_off + y * t.src_sy + z * t.src_sz + c
 
 
-def run_tables(grids, fields_per_rank, hws, dims, mode, epoch=7, direct=False):
+def run_tables(grids, fields_per_rank, hws, dims, mode, epoch=7, direct=False, host=False):
     n = len(grids)
     mem = [[flat_bytes(A) for A in fr] for fr in fields_per_rank]
-    tables, stagings = [], []
+    tables, stagings, caches = [], [], []
     for r, g in enumerate(grids):
         cf = [L.make_field(0x10000 * (i + 1), A.shape, hws[i], A.dtype.itemsize) for i, A in enumerate(fields_per_rank[r])]
-        tiles, stg = L.plan_tiles(desc_of(g), cf, dims, mode | (0x100 if direct else 0))
-        tables.append(tiles)
+        tiles, stg = L.plan_tiles(desc_of(g), cf, dims, mode | (0x100 if direct else 0) | (0x200 if host else 0))
+        tables.append([t for t in tiles if t.kind not in (WRAP_LINES, HOST_LINES_X)])
         stagings.append(np.full(max(stg, 1), 0xEE, dtype=np.uint8))
+        # host fields: whole-line tiles.  x self-wraps run on their own; exchanged x-faces are fetched into a cache
+        # that the exchange tiles address as extra fields (one per host field with such faces, in field order).
+        hx = [t for t in tiles if t.kind == HOST_LINES_X]
+        cache = np.full(max([t.dst_sy + (t.row0 + t.nrows) * 128 for t in hx], default=0), 0xCC, dtype=np.uint8)
+        for t in tiles:
+            if t.kind == WRAP_LINES:
+                wrap_lines(t, mem[r][t.field])
+        for t in hx:
+            host_lines(t, mem[r][t.field], cache, False)
+        seen = []
+        for t in hx:
+            if t.field not in seen:
+                seen.append(t.field)
+                mem[r].append(cache[t.dst_sy:])
+        caches.append((hx, cache))
     kinds = {t.kind for tb in tables for t in tb}
     assert kinds <= ({PUSH_LL, LOCAL, WRAPX, UNPACK_LL} if mode == L.IGG_MODE_IPC_LL128 else {PUSH, LOCAL, WRAPX, UNPACK}) | ({PUSH_DIRECT, WAIT} if direct else set())
     ep = np.frombuffer(np.uint64(epoch).tobytes(), dtype=np.uint8)
@@ -112,6 +155,10 @@ def run_tables(grids, fields_per_rank, hws, dims, mode, epoch=7, direct=False):
                     for pb in range(line * PAYLOAD, min(line * PAYLOAD + PAYLOAD, nbytes), W):
                         d = box_offset(t, pb)
                         mem[r][t.field][d:d + W] = stg[base + pb - line * PAYLOAD: base + pb - line * PAYLOAD + W]
+    for r in range(n):                                  # host fields: the cached lines go back whole
+        hx, cache = caches[r]
+        for t in hx:
+            host_lines(t, mem[r][t.field], cache, True)
     # every line of every LL slot that is read was written exactly once per call: count lines
     if mode == L.IGG_MODE_IPC_LL128:
         for r, g in enumerate(grids):
@@ -277,3 +324,39 @@ def test_direct_to_halo_tile_tables_match_oracle(case, mode):
     tiles, _ = L.plan_tiles(desc_of(grids[0]), cf, dims, mode | 0x100)
     wide = shapes[0][0] * elsize >= 1024 and (grids[0].dims[1] > 1 or grids[0].dims[2] > 1)     # a y or z neighbour is another rank
     assert any(t.kind == PUSH_DIRECT for t in tiles) == wide
+
+
+HOST_CASES = [
+    # rows on 64-byte boundaries: x-faces through whole lines (wrapped: kind 5; exchanged: kind 11 + cache fields)
+    (2, (16, 9, 10), dict(periodx=1, periody=1, periodz=1), [(16, 9, 10), (24, 9, 10)], None, 8, (3, 1, 2)),
+    (2, (32, 9, 10), dict(overlaps=(4, 2, 2), halowidths=(2, 1, 1)), [(32, 9, 10), (32, 10, 10), (33, 9, 10)], None, 4, (3, 1, 2)),
+    (8, (16, 9, 10), dict(periodx=1, periodz=1), [(16, 9, 10)], None, 8, (3, 1, 2)),
+    (4, (64, 12, 1), dict(periodx=1, periody=1, overlaps=(4, 2, 2), halowidths=(2, 1, 1)), [(64, 12), (64, 13)], None, 2, (3, 1, 2)),
+    (1, (16, 9, 10), dict(periodx=1, periody=1, periodz=1), [(16, 9, 10)], None, 8, (3, 1, 2)),
+    (2, (16, 9, 10), dict(dimx=1, dimy=2, periodx=1, periody=1, periodz=1), [(16, 9, 10)], None, 8, (3, 1, 2)),
+    (3, (16, 9, 10), dict(), [(16, 9, 10)], None, 8, (1,)),                     # non-periodic: edge ranks exchange one end only
+    (2, (13, 9, 10), dict(periodx=1, periody=1, periodz=1), [(13, 9, 10)], None, 8, (3, 1, 2)),     # rows not aligned: per cell
+]
+
+
+@pytest.mark.parametrize("mode", [L.IGG_MODE_IPC_1PHASE, L.IGG_MODE_IPC_LL128], ids=["fence", "ll128"])
+@pytest.mark.parametrize("case", HOST_CASES, ids=[f"h{i}" for i in range(len(HOST_CASES))])
+def test_host_field_tile_tables_match_oracle(case, mode):
+    """Fields in page-locked host memory: x self-wraps and exchanged x-faces through whole 64-byte lines."""
+    nprocs, gsz, kw, shapes, hws, elsize, dims = case
+    grids = O.make_grids(nprocs, *gsz, **kw)
+    hws = hws or [grids[0].halowidths] * len(shapes)
+    base = [[rand_field(s, elsize, 3000 * r + 10 * i + 7) for i, s in enumerate(shapes)] for r in range(nprocs)]
+    want = [[a.copy(order="F") for a in fr] for fr in base]
+    O.update_halo(grids, [[(a, hws[i]) for i, a in enumerate(fr)] for fr in want], dims=dims)
+    got = [[a.copy(order="F") for a in fr] for fr in base]
+    run_tables(grids, got, hws, dims, mode, host=True)
+    for r in range(nprocs):
+        for i in range(len(shapes)):
+            assert np.array_equal(flat_bytes(got[r][i]), flat_bytes(want[r][i])), (r, i)
+    cf = [L.make_field(0x10000 * (i + 1), s, hws[i], elsize) for i, s in enumerate(shapes)]
+    tiles, _ = L.plan_tiles(desc_of(grids[0]), cf, dims, mode | 0x200)
+    aligned = shapes[0][0] * elsize % 64 == 0
+    x_remote, x_self = grids[0].dims[0] > 1, grids[0].dims[0] == 1 and grids[0].periods[0]
+    assert any(t.kind == HOST_LINES_X for t in tiles) == (aligned and x_remote and 1 in dims)
+    assert any(t.kind == WRAP_LINES for t in tiles) == (aligned and bool(x_self) and 1 in dims)
