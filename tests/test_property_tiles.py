@@ -1,6 +1,7 @@
 """Randomised check of the tile tables (hypothesis): for random process grids, periodicities, overlaps, halowidths,
 field shapes (staggered up and down, narrow and wide in x), element sizes, pointer alignments and `dims=` orders,
-with and without symmetric fields (direct-to-halo), the tile tables of both IPC protocols -- executed on the CPU as
+fields in device memory, in symmetric allocations (direct-to-halo) and in page-locked host memory (whole-line
+x-faces), the tile tables of both IPC protocols -- executed on the CPU as
 the kernels address memory (tests/test_tiles_cpu.py) -- give exactly what the oracle's three dependent phases give.
 No GPU needed."""
 import numpy as np
@@ -22,6 +23,8 @@ def configs(draw):
     n = [draw(st.integers(ol[d] + 2 * hw[d] + 1, ol[d] + 2 * hw[d] + 7)) if d < ndim else 1 for d in range(3)]
     if draw(st.booleans()):
         n[0] += 128          # rows of 1 KiB and more (with 8-byte elements): wide enough for direct-to-halo
+    if draw(st.booleans()):
+        n[0] = (n[0] + 15) // 16 * 16      # rows on 64-byte boundaries: host fields take their x-faces through whole lines
     nf = draw(st.integers(1, 3))
     shapes = []
     for _ in range(nf):
@@ -33,9 +36,10 @@ def configs(draw):
     return dims, periods, hw, ol, n, shapes, elsize, order, seed
 
 
-@settings(max_examples=60, deadline=None, suppress_health_check=[HealthCheck.too_slow, HealthCheck.data_too_large])
-@given(configs(), st.sampled_from([L.IGG_MODE_IPC_1PHASE, L.IGG_MODE_IPC_LL128, L.IGG_MODE_IPC_AUTO]), st.booleans())
-def test_random_tile_tables_match_oracle(cfg, mode, direct):
+@settings(max_examples=90, deadline=None, suppress_health_check=[HealthCheck.too_slow, HealthCheck.data_too_large])
+@given(configs(), st.sampled_from([L.IGG_MODE_IPC_1PHASE, L.IGG_MODE_IPC_LL128, L.IGG_MODE_IPC_AUTO]),
+       st.sampled_from(["device", "symmetric", "host"]))
+def test_random_tile_tables_match_oracle(cfg, mode, where):
     dims, periods, hw, ol, n, shapes, elsize, order, seed = cfg
     nprocs = dims[0] * dims[1] * dims[2]
     try:
@@ -53,7 +57,7 @@ def test_random_tile_tables_match_oracle(cfg, mode, direct):
         return                                           # e.g. a field without any halo: rejected by check_fields
     got = [[a.copy(order="F") for a in fr] for fr in base]
     auto = mode == L.IGG_MODE_IPC_AUTO                    # (small calls: auto = LL128 tiles)
-    run_tables(grids, got, hws, order, L.IGG_MODE_IPC_LL128 if auto else mode, direct=direct)
+    run_tables(grids, got, hws, order, L.IGG_MODE_IPC_LL128 if auto else mode, direct=where == "symmetric", host=where == "host")
     for r in range(nprocs):
         for i in range(len(shapes)):
             assert np.array_equal(flat_bytes(got[r][i]), flat_bytes(want[r][i])), (r, i)
