@@ -129,6 +129,7 @@ struct igg_ctx {
     int64_t  region_cap[2][IGG_NOFFSETS] = {{0}}, region_off[2][IGG_NOFFSETS] = {{0}};
     uint32_t flag_cap[IGG_NOFFSETS] = {0}, flag_off[IGG_NOFFSETS] = {0};
     char* hostx_cache = nullptr; int64_t hostx_cache_cap = 0;     // row-end lines of host-resident fields (exchanged x-faces)
+    std::vector<char*> hostx_old_caches;        // outgrown caches (captured launches may still use them)
     cudaStream_t side_stream = nullptr;         // host-resident fields: the wrap-lines kernel runs beside the exchange
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     unsigned long long timeout_ns = 20ull * 1000000000ull;
@@ -628,6 +629,7 @@ int igg_destroy(igg_ctx* ctx) {
     for (auto& p : ctx->peers) { close_segment(p.ctrl); close_segment(p.staging); close_segment(p.gather); }
     for (auto& pl : ctx->plans) { cudaFree(pl->d_plan); cudaFree(pl->d_wrap_tiles); cudaFree(pl->d_hostx_tiles); }
     if (ctx->hostx_cache) cudaFree(ctx->hostx_cache);
+    for (char* c : ctx->hostx_old_caches) cudaFree(c);
     for (auto& reg : ctx->regs) { for (auto& ps : reg.peer) close_segment(ps); }
     if (ctx->g.nprocs > 1 && ctx->cp.attached() && !ctx->regs.empty()) ctx->cp.barrier();   // mappings closed before the frees
     for (auto& reg : ctx->regs) if (reg.base) cudaFree(reg.base);
@@ -900,8 +902,11 @@ static int launch_plan(igg_ctx* ctx, Plan* plan, int nfields, const igg_field* f
         // Exchanged x-faces of host-resident fields: fetch the row-end lines into the device cache; the exchange
         // kernel sees every such field's lines as one more field (index nfields + k).
         if (plan->hostx_cache_bytes > ctx->hostx_cache_cap) {
-            CU(cudaDeviceSynchronize());
-            if (ctx->hostx_cache) { CU(cudaFree(ctx->hostx_cache)); ctx->hostx_cache = nullptr; }
+            // A bigger cache is a new allocation; the old one stays until igg_destroy: launches recorded into a CUDA
+            // graph keep using the cache they were captured with (all three kernels of a call carry the same pointer).
+            if (ctx->hostx_cache) ctx->hostx_old_caches.push_back(ctx->hostx_cache);
+            ctx->hostx_cache = nullptr;
+            ctx->hostx_cache_cap = 0;
             CU(cudaMalloc(&ctx->hostx_cache, (size_t)plan->hostx_cache_bytes));
             ctx->hostx_cache_cap = plan->hostx_cache_bytes;
         }
