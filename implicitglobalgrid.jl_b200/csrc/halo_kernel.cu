@@ -13,8 +13,10 @@
 // self-copy and the 12 host-blocking stream synchronisations per field
 // (ref: src/CUDAExt/update_halo.jl:153-259, src/update_halo.jl:51-88).
 //
+//   PUSH_DIRECT / WAIT  fields in symmetric allocations: a send box that spans x goes straight into the neighbour's
+//          halo (after its "ready" word), the receiver only waits for the arrival flags.
 // Work is cut into tiles (TileRec, built on the host in plan.cpp); block b handles tiles b, b+grid, ...  Tiles are
-// ordered PUSH, LOCAL, UNPACK, so every block finishes (and flags) its pushes before it may spin on a flag.
+// ordered PUSH, LOCAL, WRAPX, UNPACK, so every block finishes (and flags) its pushes before it may spin on a flag.
 // The grid never exceeds the number of co-resident blocks, so spinning blocks cannot starve pushing ones.
 //
 // Pure data movement: bytes are copied as opaque 1/2/4/8/16-byte words, so results are bit-exact for any element
